@@ -1,0 +1,484 @@
+// Per-knot evaluation of the soft-actuated action model: one call = what one thread computes.
+//
+//   knot_eval<N, NU, VSA, false>  ==  IntegratedActionModelEulerASR.calc      (xnext, cost)
+//   knot_eval<N, NU, VSA, true>   ==  ....calc + ....calcDiff                 (+ the derivative record)
+//
+// Reference arithmetic being replaced (file:line under /root/reference/python/aslr_to):
+//   integrated_action.py:13-42, free_fwddyn_asr.py:20-92, free_fwddyn_vsa.py:20-94,
+//   actuation_asr.py:9-13, residual_frame_placement.py:13-24, stiffness_cost.py:13-20,
+//   __init__.py:229-249 (double-pendulum cost), statemultibody_aslr.py:32-61 (vector-space state),
+// plus the pinocchio / crocoddyl pieces those call (SURVEY.md Appendices A.5 and B).
+//
+// Rigid-body algorithm (ours, B200-first rather than pinocchio's): everything is expressed in the
+// world frame, so after one forward-kinematics pass the RNEA / CRBA recursions and their tangents are
+// plain sums without per-joint transforms, all in registers for small N:
+//   v_i = v_{i-1} + S_i qd_i                 a_i = a_{i-1} + S_i qdd_i + v_{i-1} x S_i qd_i,  a_{-1} = -g
+//   f_i = Y_i a_i + v_i x* Y_i v_i           tau_i = S_i . sum_{k>=i} f_k
+//   M_ij = S_j . (sum_{k>=i} Y_k) S_i (j<=i)
+// d tau / dq_j and d tau / dqd_j are obtained by propagating tangents of (v, a, f) down the chain using
+//   dS_i/dq_j = S_j x S_i (j<i),   dY_i/dq_j = S_j x* Y_i - Y_i S_j x (j<=i).
+#pragma once
+
+#include "problem_dev.cuh"
+#include "se3log.cuh"
+
+namespace aslr {
+
+template <int N>
+struct CostAcc {
+  double Lx[4 * N];
+  double Lu[2 * N];
+  double Lqq[N * N];    // dense block of Lxx on (q_l, q_l)
+  double Lxxd[4 * N];   // diagonal contributions to Lxx
+  double Luud[2 * N];   // diagonal contributions to Luu
+};
+
+// Y_i-derivative applied to a motion m:  (S x* (Y m)) - Y (S x m), with Ym = Y m precomputed
+ASLR_HD SV dY_mul(const SI& Y, SV S, SV m, SV Ym) { return cross_mf(S, Ym) - mul(Y, cross_mm(S, m)); }
+
+template <int N, int NU, bool VSA, bool DIFF>
+ASLR_HD void knot_eval(const DevProblem<N>& P, const DevCostSum<N>& C, const double dt, const double* x,
+                       const double* u, const double* Kocp, const double* mref, double* xnext, double& cost_out,
+                       double* rec, double* xout, double* dFx, double* dFu) {
+  constexpr int NX = 4 * N;
+  const double* ql = x;
+  const double* qm = x + N;
+  const double* vl = x + 2 * N;
+  const double* vm = x + 3 * N;
+
+  // ---------------------------------------------------------------- forward kinematics, world frame
+  M3 R[N];
+  V3 p[N];
+  SV S[N];
+  SI Y[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    double s, c;
+    sincos(ql[i], &s, &c);
+    const double omc = 1.0 - c;
+    M3 Rl;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) Rl.m[k] = P.j[i].A0[k] + s * P.j[i].A1[k] + omc * P.j[i].A2[k];
+    if (i == 0) {
+      R[0] = Rl;
+      p[0] = ld3(P.j[0].p);
+    } else {
+      R[i] = mul(R[i - 1], Rl);
+      p[i] = p[i - 1] + mul(R[i - 1], ld3(P.j[i].p));
+    }
+    const V3 z = mul(R[i], ld3(P.j[i].axis));
+    S[i] = SV{cross(p[i], z), z};
+    Y[i] = world_inertia(P.j[i].mass, ld3(P.j[i].com), ldm3(P.j[i].Ic), R[i], p[i]);
+  }
+
+  // ---------------------------------------------------------------- RNEA with qdd = 0 -> nle ; CRBA -> M
+  SV v[N], a[N], f[N], Yv[N];
+  {
+    SV vp = sv_zero();
+    SV ap = SV{V3{-P.g[0], -P.g[1], -P.g[2]}, V3{0, 0, 0}};
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      const SV Sq = vl[i] * S[i];
+      v[i] = vp + Sq;
+      a[i] = (i == 0) ? ap : ap + cross_mm(vp, Sq);
+      Yv[i] = mul(Y[i], v[i]);
+      f[i] = mul(Y[i], a[i]) + cross_mf(v[i], Yv[i]);
+      vp = v[i];
+      ap = a[i];
+    }
+  }
+  double M[N * N], nle[N];
+  {
+    SV F = sv_zero();
+    SI Yc = Y[N - 1];
+#pragma unroll
+    for (int i = N - 1; i >= 0; --i) {
+      F = F + f[i];
+      nle[i] = dot(S[i], F);
+      if (i != N - 1) Yc = Yc + Y[i];
+      const SV Fc = mul(Yc, S[i]);
+#pragma unroll
+      for (int j = 0; j <= i; ++j) {
+        const double mij = dot(S[j], Fc);
+        M[i * N + j] = mij;
+        M[j * N + i] = mij;
+      }
+    }
+  }
+
+  // ---------------------------------------------------------------- elastic coupling and accelerations
+  double dq[N], tauc[N], Kmat[N * N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) dq[i] = ql[i] - qm[i];
+  if (VSA) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) tauc[i] = u[N + i] * dq[i];  // K = diag(u[n:]), free_fwddyn_vsa.py:34-37
+  } else {
+#pragma unroll
+    for (int i = 0; i < N * N; ++i) Kmat[i] = Kocp ? Kocp[i] : P.K[i];
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      double s = 0;
+#pragma unroll
+      for (int k = 0; k < N; ++k) s += Kmat[i * N + k] * dq[k];
+      tauc[i] = s;  // free_fwddyn_asr.py:35
+    }
+  }
+  double L[N * N];
+#pragma unroll
+  for (int i = 0; i < N * N; ++i) L[i] = M[i];
+  cholesky<N>(L);
+  double al[N], am[N], Minv[DIFF ? N * N : 1];
+  if (DIFF) {
+    // explicit inverse, as the reference does (free_fwddyn_asr.py:40)
+#pragma unroll
+    for (int c = 0; c < N; ++c) {
+      double e[N];
+#pragma unroll
+      for (int k = 0; k < N; ++k) e[k] = (k == c) ? 1.0 : 0.0;
+      chol_solve<N>(L, e);
+#pragma unroll
+      for (int k = 0; k < N; ++k) Minv[k * N + c] = e[k];
+    }
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      double s = 0;
+#pragma unroll
+      for (int k = 0; k < N; ++k) s += Minv[i * N + k] * (-nle[k] - tauc[k]);
+      al[i] = s;  // free_fwddyn_asr.py:43 (tau[:n] is zero for every shipped actuation)
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < N; ++i) al[i] = -nle[i] - tauc[i];
+    chol_solve<N>(L, al);
+  }
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    double tm = tauc[i];
+#pragma unroll
+    for (int k = 0; k < N; ++k) tm += P.Sm[i * N + k] * u[k];  // tau[n:] = Sm u[:n]
+    tauc[i] = tm;  // now motor-side generalised force tau_m + tau_couple
+  }
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < N; ++k) s += P.Binv[i * N + k] * tauc[k];
+    am[i] = s;  // free_fwddyn_asr.py:46
+  }
+
+  // ---------------------------------------------------------------- semi-implicit Euler step
+  // dx = [v dt + a dt^2, a dt]; xnext = x + dx   (integrated_action.py:23-24)
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    xnext[i] = ql[i] + (vl[i] * dt + al[i] * dt * dt);
+    xnext[N + i] = qm[i] + (vm[i] * dt + am[i] * dt * dt);
+    xnext[2 * N + i] = vl[i] + al[i] * dt;
+    xnext[3 * N + i] = vm[i] + am[i] * dt;
+  }
+  if (xout) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) xout[i] = al[i], xout[N + i] = am[i];
+  }
+
+  // ---------------------------------------------------------------- costs (crocoddyl.CostModelSum)
+  double cost = 0.0;
+  CostAcc<N> acc;
+  if (DIFF) {
+#pragma unroll
+    for (int i = 0; i < NX; ++i) acc.Lx[i] = 0, acc.Lxxd[i] = 0;
+#pragma unroll
+    for (int i = 0; i < 2 * N; ++i) acc.Lu[i] = 0, acc.Luud[i] = 0;
+#pragma unroll
+    for (int i = 0; i < N * N; ++i) acc.Lqq[i] = 0;
+  }
+#pragma unroll 1
+  for (int k = 0; k < C.nterms; ++k) {
+    const DevCostTerm<N>& t = C.t[k];
+    const double w = t.weight;
+    if (t.kind == ASLR_COST_FRAME_PLACEMENT) {
+      // residual_frame_placement.py:13-24
+      M3 Rp = R[0];
+      V3 pp = p[0];
+#pragma unroll
+      for (int i = 1; i < N; ++i)
+        if (i == t.frame_parent) Rp = R[i], pp = p[i];
+      const M3 Rf = mul(Rp, ldm3(t.fR));
+      const V3 pf = pp + mul(Rp, ld3(t.fp));
+      const double* rf = mref ? mref : t.ref;
+      const M3 Rref = ldm3(rf);
+      const M3 Rr = mulTN(Rref, Rf);
+      const V3 pr = mulT(Rref, pf - ld3(rf + 9));
+      double r[6], theta;
+      V3 wv;
+      se3_log(Rr, pr, r, wv, theta);
+      double c = 0;
+#pragma unroll
+      for (int i = 0; i < 6; ++i) c += t.act[i] * r[i] * r[i];
+      cost += w * (0.5 * c);
+      if (DIFF) {
+        M3 A, CA;
+        se3_jlog(wv, theta, pr, A, CA);
+        double J[6 * N];
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const bool on = (j <= t.frame_parent);
+          const V3 ang = mulT(Rf, S[j].a);
+          const V3 lin = mulT(Rf, S[j].l + cross(S[j].a, pf));
+          const V3 jl = mul(A, lin) + mul(CA, ang);
+          const V3 ja = mul(A, ang);
+          J[0 * N + j] = on ? jl.x : 0.0, J[1 * N + j] = on ? jl.y : 0.0, J[2 * N + j] = on ? jl.z : 0.0;
+          J[3 * N + j] = on ? ja.x : 0.0, J[4 * N + j] = on ? ja.y : 0.0, J[5 * N + j] = on ? ja.z : 0.0;
+        }
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+          double g = 0;
+#pragma unroll
+          for (int m = 0; m < 6; ++m) g += J[m * N + i] * (t.act[m] * r[m]);
+          acc.Lx[i] += w * g;
+#pragma unroll
+          for (int j = 0; j < N; ++j) {
+            double h = 0;
+#pragma unroll
+            for (int m = 0; m < 6; ++m) h += J[m * N + i] * (t.act[m] * J[m * N + j]);
+            acc.Lqq[i * N + j] += w * h;
+          }
+        }
+      }
+    } else if (t.kind == ASLR_COST_STATE) {
+      // ResidualModelState: r = diff(xref, x) = x - xref; weighted-quad activation
+      double c = 0;
+#pragma unroll
+      for (int i = 0; i < NX; ++i) {
+        const double r = x[i] - t.ref[i];
+        c += t.act[i] * r * r;
+        if (DIFF) acc.Lx[i] += w * (t.act[i] * r), acc.Lxxd[i] += w * t.act[i];
+      }
+      cost += w * (0.5 * c);
+    } else if (t.kind == ASLR_COST_CONTROL) {
+      double c = 0;
+#pragma unroll
+      for (int i = 0; i < NU; ++i) {
+        const double r = u[i] - t.ref[i];
+        c += t.act[i] * r * r;
+        if (DIFF) acc.Lu[i] += w * (t.act[i] * r), acc.Luud[i] += w * t.act[i];
+      }
+      cost += w * (0.5 * c);
+    } else if (t.kind == ASLR_COST_STIFFNESS) {
+      // linear cost sum(lamda (sigma - sigma_ref)), stiffness_cost.py:13-20
+      double c = 0;
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        if (NU > N) c += t.act[0] * (u[(NU > N ? N : 0) + i] - t.ref[i]);
+        if (DIFF && NU > N) acc.Lu[(NU > N ? N : 0) + i] += w * t.act[0];
+      }
+      cost += w * c;
+    } else if (t.kind == ASLR_COST_DOUBLE_PENDULUM) {
+      // python/aslr_to/__init__.py:229-249 (n = 2 only; checked at problem creation)
+      if (N == 2) {
+        double s1, c1, s2, c2;
+        sincos(x[0], &s1, &c1);
+        sincos(x[1], &s2, &c2);
+        const double r0 = s1, r1 = s2, r2 = 1 + c1, r3 = 1 + c2, r4 = x[NX > 4 ? 4 : 0], r5 = x[NX > 5 ? 5 : 0];
+        const double* aw = t.act;
+        cost += w * (0.5 * (aw[0] * r0 * r0 + aw[1] * r1 * r1 + aw[2] * r2 * r2 + aw[3] * r3 * r3 + aw[4] * r4 * r4 +
+                            aw[5] * r5 * r5));
+        if (DIFF) {
+          acc.Lx[0] += w * (c1 * (aw[0] * r0) - s1 * (aw[2] * r2));
+          acc.Lx[1] += w * (c2 * (aw[1] * r1) - s2 * (aw[3] * r3));
+          acc.Lx[NX > 4 ? 4 : 0] += w * (aw[4] * r4);
+          acc.Lx[NX > 5 ? 5 : 0] += w * (aw[5] * r5);
+          // the reference's diagonal pseudo-Hessian (from the 1 - cos variant), reproduced verbatim
+          acc.Lxxd[0] += w * ((c1 * c1 - s1 * s1) * aw[0] + (s1 * s1 + (1 - c1) * c1) * aw[2]);
+          acc.Lxxd[1] += w * ((c2 * c2 - s2 * s2) * aw[1] + (s2 * s2 + (1 - c2) * c2) * aw[3]);
+          acc.Lxxd[NX > 4 ? 4 : 0] += w * aw[4];
+          acc.Lxxd[NX > 5 ? 5 : 0] += w * aw[5];
+        }
+      }
+    }
+  }
+  cost_out = cost;  // NOT scaled by dt (integrated_action.py:19)
+  if (!DIFF) return;
+
+  // ---------------------------------------------------------------- inverse-dynamics tangents at (q, v, a_l)
+  // (what pinocchio.computeRNEADerivatives provides to free_fwddyn_asr.py:75)
+  SV Ya[N], F[N];
+  {
+    SV ac = sv_zero();
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      ac = ac + al[i] * S[i];
+      a[i] = a[i] + ac;
+      Ya[i] = mul(Y[i], a[i]);
+      f[i] = Ya[i] + cross_mf(v[i], Yv[i]);
+    }
+    SV Fs = sv_zero();
+#pragma unroll
+    for (int i = N - 1; i >= 0; --i) {
+      Fs = Fs + f[i];
+      F[i] = Fs;
+    }
+  }
+  double dtq[N * N], dtv[N * N];
+#pragma unroll(N <= 3 ? N : 1)
+  for (int j = 0; j < N; ++j) {
+    SV df[N];
+    // ---- d/dq_j
+    {
+      const SV Sj = S[j];
+      SV dvp = sv_zero(), dap = sv_zero();
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        if (i < j) {
+          df[i] = sv_zero();
+        } else if (i == j) {
+          const SV dYa = dY_mul(Y[i], Sj, a[i], Ya[i]);
+          const SV dYv = dY_mul(Y[i], Sj, v[i], Yv[i]);
+          df[i] = dYa + cross_mf(v[i], dYv);
+        } else {
+          const SV SjSi = cross_mm(Sj, S[i]);
+          const SV dvi = dvp + vl[i] * SjSi;
+          const SV dai = dap + al[i] * SjSi + vl[i] * (cross_mm(dvp, S[i]) + cross_mm(v[i - 1], SjSi));
+          const SV dYa = dY_mul(Y[i], Sj, a[i], Ya[i]);
+          const SV dYv = dY_mul(Y[i], Sj, v[i], Yv[i]);
+          df[i] = dYa + mul(Y[i], dai) + cross_mf(dvi, Yv[i]) + cross_mf(v[i], dYv + mul(Y[i], dvi));
+          dvp = dvi;
+          dap = dai;
+        }
+      }
+      SV dF = sv_zero();
+#pragma unroll
+      for (int i = N - 1; i >= 0; --i) {
+        if (i >= j) dF = dF + df[i];
+        double t = dot(S[i], dF);
+        if (i > j) t += dot(cross_mm(Sj, S[i]), F[i]);
+        dtq[i * N + j] = t;
+      }
+    }
+    // ---- d/dqd_j
+    {
+      const SV Sj = S[j];
+      SV dap = sv_zero();
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        if (i < j) {
+          df[i] = sv_zero();
+        } else {
+          SV dai;
+          if (i == j)
+            dai = (i == 0) ? sv_zero() : cross_mm(v[i > 0 ? i - 1 : 0], Sj);
+          else
+            dai = dap + vl[i] * cross_mm(Sj, S[i]);
+          df[i] = mul(Y[i], dai) + cross_mf(Sj, Yv[i]) + cross_mf(v[i], mul(Y[i], Sj));
+          dap = dai;
+        }
+      }
+      SV dF = sv_zero();
+#pragma unroll
+      for (int i = N - 1; i >= 0; --i) {
+        if (i >= j) dF = dF + df[i];
+        dtv[i * N + j] = dot(S[i], dF);
+      }
+    }
+  }
+
+  // ---------------------------------------------------------------- differential-model Jacobians
+  // AX = d[a_l; a_m]/d[q_l q_m v_l] (2N x 3N; the v_m columns are identically zero, there is no
+  // motor-side damping), AU = d[a_l; a_m]/du
+  if (VSA) {
+#pragma unroll
+    for (int i = 0; i < N * N; ++i) Kmat[i] = 0.0;
+#pragma unroll
+    for (int i = 0; i < N; ++i) Kmat[i * N + i] = u[N + i];
+  }
+  double AX[2 * N * 3 * N], AU[2 * N * NU];
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+#pragma unroll
+    for (int c = 0; c < N; ++c) {
+      double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+#pragma unroll
+      for (int k = 0; k < N; ++k) {
+        s0 += Minv[i * N + k] * (-dtq[k * N + c] - Kmat[k * N + c]);  // free_fwddyn_asr.py:78,81
+        s1 += Minv[i * N + k] * Kmat[k * N + c];                       // :82
+        s2 += Minv[i * N + k] * (-dtv[k * N + c]);                     // :79,83
+        s3 += P.Binv[i * N + k] * Kmat[k * N + c];                     // :85
+      }
+      AX[i * 3 * N + c] = s0;
+      AX[i * 3 * N + N + c] = s1;
+      AX[i * 3 * N + 2 * N + c] = s2;
+      AX[(N + i) * 3 * N + c] = s3;
+      AX[(N + i) * 3 * N + N + c] = -s3;  // :86
+      AX[(N + i) * 3 * N + 2 * N + c] = 0.0;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 2 * N * NU; ++i) AU[i] = 0.0;
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+#pragma unroll
+    for (int c = 0; c < N; ++c) {
+      double bs = 0;
+#pragma unroll
+      for (int k = 0; k < N; ++k) bs += P.Binv[i * N + k] * P.Sm[k * N + c];
+      if (VSA) {
+        AU[(N + i) * NU + c] = bs;                                      // free_fwddyn_vsa.py:92
+        AU[i * NU + (NU > N ? N : 0) + c] = Minv[i * N + c] * (-dq[c]);           // :89
+        AU[(N + i) * NU + (NU > N ? N : 0) + c] = P.Binv[i * N + c] * dq[c];      // :90
+      } else {
+        AU[(N + i) * NU + c] = P.write_fu ? bs : 0.0;                   // free_fwddyn_asr.py:88-89
+      }
+    }
+  }
+  if (dFx) {
+#pragma unroll
+    for (int r = 0; r < 2 * N; ++r)
+#pragma unroll
+      for (int c = 0; c < NX; ++c) dFx[r * NX + c] = (c < 3 * N) ? AX[r * 3 * N + (c < 3 * N ? c : 0)] : 0.0;
+  }
+  if (dFu) {
+#pragma unroll
+    for (int i = 0; i < 2 * N * NU; ++i) dFu[i] = AU[i];
+  }
+  if (!rec) return;
+
+  // ---------------------------------------------------------------- action-model record
+  // Fx = I + dt [[dt a_x + [0 I]], [a_x]],  Fu = [dt^2 a_u; dt a_u]   (integrated_action.py:31-37);
+  // L* copied unscaled (integrated_action.py:38-42)
+  typedef Rec<NX, NU> RC;
+  const double dt2 = dt * dt;
+#pragma unroll
+  for (int r = 0; r < 2 * N; ++r) {
+#pragma unroll
+    for (int c = 0; c < NX; ++c) {
+      const double ax = (c < 3 * N) ? AX[r * 3 * N + (c < 3 * N ? c : 0)] : 0.0;
+      rec[RC::FX + r * NX + c] = ((r == c) ? 1.0 : 0.0) + dt2 * ax + ((c == r + 2 * N) ? dt : 0.0);
+      rec[RC::FX + (2 * N + r) * NX + c] = ((2 * N + r == c) ? 1.0 : 0.0) + dt * ax;
+    }
+#pragma unroll
+    for (int c = 0; c < NU; ++c) {
+      rec[RC::FU + r * NU + c] = dt2 * AU[r * NU + c];
+      rec[RC::FU + (2 * N + r) * NU + c] = dt * AU[r * NU + c];
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < NX; ++r) {
+#pragma unroll
+    for (int c = 0; c < NX; ++c) {
+      double val = (r == c) ? acc.Lxxd[r] : 0.0;
+      if (r < N && c < N) val += acc.Lqq[(r < N ? r : 0) * N + (c < N ? c : 0)];
+      rec[RC::LXX + r * NX + c] = val;
+    }
+#pragma unroll
+    for (int c = 0; c < NU; ++c) rec[RC::LXU + r * NU + c] = 0.0;  // no cost of the menu couples x and u
+    rec[RC::LX + r] = acc.Lx[r];
+  }
+#pragma unroll
+  for (int r = 0; r < NU; ++r) {
+#pragma unroll
+    for (int c = 0; c < NU; ++c) rec[RC::LUU + r * NU + c] = (r == c) ? acc.Luud[r] : 0.0;
+    rec[RC::LU + r] = acc.Lu[r];
+  }
+}
+
+}  // namespace aslr
