@@ -1,0 +1,460 @@
+// K2: Riccati backward pass of one OCP, sequential in time, cooperative over a thread group
+// (a warp for nx = 8, a CTA for nx = 28).  SolverDDP::backwardPass / computeGains,
+// SolverBoxDDP::computeGains + BoxQP::solve, SolverFDDP::updateExpectedImprovement,
+// SolverDDP::expectedImprovement / stoppingCriteria and the regularisation retry loop of
+// SolverDDP::solve.
+#pragma once
+
+#include "solver_dev.cuh"
+
+namespace aslr {
+
+// thread-group policies -----------------------------------------------------------------------
+struct GrpSerial {  // host emulation: one thread plays the whole group
+  static constexpr int G = 1;
+  int lane;
+  ASLR_HD void sync() const {}
+};
+#if defined(__CUDACC__)
+struct GrpWarp {
+  static constexpr int G = 32;
+  int lane;
+  __device__ __forceinline__ void sync() const { __syncwarp(); }
+};
+template <int THREADS>
+struct GrpCta {
+  static constexpr int G = THREADS;
+  int lane;
+  __device__ __forceinline__ void sync() const { __syncthreads(); }
+};
+#endif
+
+// shared-memory carve-up for one group (all sizes in doubles)
+template <int NX, int NU>
+struct BwdSmem {
+  static constexpr int VXX = 0;
+  static constexpr int FX = VXX + NX * NX;
+  static constexpr int QXX = FX + NX * NX;
+  static constexpr int A = QXX + NX * NX;  // Fx^T Vxx, later the unsymmetrised Vxx
+  static constexpr int FU = A + NX * NX;
+  static constexpr int QXU = FU + NX * NU;
+  static constexpr int FUV = QXU + NX * NU;  // Fu^T Vxx
+  static constexpr int KG = FUV + NU * NX;
+  static constexpr int QUU = KG + NU * NX;
+  static constexpr int LC = QUU + NU * NU;  // Cholesky factor of Quu / Quu_inv for the box QP
+  static constexpr int VX = LC + NU * NU;
+  static constexpr int QX = VX + NX;
+  static constexpr int FS = QX + NX;
+  static constexpr int W = FS + NX;
+  static constexpr int QU = W + NX;
+  static constexpr int KF = QU + NU;
+  static constexpr int QUUK = KF + NU;
+  static constexpr int RED = QUUK + NU;       // reduction scratch, 2 * G' doubles (G' <= 128)
+  static constexpr int FLAG = RED + 2 * 128;  // [0] failure flag
+  static constexpr int SIZE = FLAG + 2;
+};
+
+// Projected-Newton box QP (Tassa 2014) as in crocoddyl's BoxQP::solve(H, q, lb, ub, xinit) with
+// maxiter 100, th_acceptstep 0.1, th_grad 1e-5, reg 0 (SolverBoxDDP ctor).  Serial: run by one
+// thread.  Outputs x, Hinv (NU x NU, zero outside free x free), clamped mask.  Returns false when a
+// free-block Cholesky fails ("backward_error").
+template <int NU>
+ASLR_HD bool boxqp_solve(const double* H, const double* q, const double* lb, const double* ub, const double* xinit,
+                         double* x, double* Hinv, bool* clamped) {
+  const double th_grad = 1e-5, th_accept = 0.1;
+  bool fact_free[NU];  // free set of the factorisation held in Hinv
+  bool have_fact = false;
+  double Lf[NU * NU];
+  for (int i = 0; i < NU; ++i) x[i] = fmax(fmin(xinit[i], ub[i]), lb[i]);
+  for (int k = 0; k < 100; ++k) {
+    double g[NU];
+    bool fr[NU];
+    int nf = 0;
+    double gnorm = 0.0;
+    for (int i = 0; i < NU; ++i) {
+      double s = q[i];
+      for (int j = 0; j < NU; ++j) s += H[i * NU + j] * x[j];
+      g[i] = s;
+    }
+    for (int j = 0; j < NU; ++j) {
+      const bool cl = (x[j] == lb[j] && g[j] > 0.0) || (x[j] == ub[j] && g[j] < 0.0);
+      clamped[j] = cl;
+      fr[j] = !cl;
+      if (!cl) {
+        ++nf;
+        gnorm = fmax(gnorm, fabs(g[j]));
+      }
+    }
+    const bool converged = (gnorm <= th_grad) || (nf == 0);
+    bool same = have_fact;
+    if (have_fact)
+      for (int j = 0; j < NU; ++j) same = same && (fact_free[j] == fr[j]);
+    if (converged && k != 0 && same) return true;
+    // factorise H[free, free] (compact indices)
+    int idx[NU];
+    int m = 0;
+    for (int j = 0; j < NU; ++j)
+      if (fr[j]) idx[m++] = j;
+    for (int i = 0; i < m; ++i)
+      for (int j = 0; j < m; ++j) Lf[i * NU + j] = H[idx[i] * NU + idx[j]];
+    for (int j = 0; j < m; ++j) {
+      double d = Lf[j * NU + j];
+      for (int c = 0; c < j; ++c) d -= Lf[j * NU + c] * Lf[j * NU + c];
+      if (d <= 0.0) return false;
+      d = sqrt(d);
+      Lf[j * NU + j] = d;
+      for (int i = j + 1; i < m; ++i) {
+        double s = Lf[i * NU + j];
+        for (int c = 0; c < j; ++c) s -= Lf[i * NU + c] * Lf[j * NU + c];
+        Lf[i * NU + j] = s / d;
+      }
+    }
+    for (int i = 0; i < NU * NU; ++i) Hinv[i] = 0.0;
+    for (int c = 0; c < m; ++c) {
+      double e[NU];
+      for (int i = 0; i < m; ++i) e[i] = (i == c) ? 1.0 : 0.0;
+      for (int i = 0; i < m; ++i) {
+        double s = e[i];
+        for (int r = 0; r < i; ++r) s -= Lf[i * NU + r] * e[r];
+        e[i] = s / Lf[i * NU + i];
+      }
+      for (int i = m - 1; i >= 0; --i) {
+        double s = e[i];
+        for (int r = i + 1; r < m; ++r) s -= Lf[r * NU + i] * e[r];
+        e[i] = s / Lf[i * NU + i];
+      }
+      for (int i = 0; i < m; ++i) Hinv[idx[i] * NU + idx[c]] = e[i];
+    }
+    have_fact = true;
+    for (int j = 0; j < NU; ++j) fact_free[j] = fr[j];
+    if (converged) return true;
+    // Newton step on the free subspace: dxf = -Hff^-1 (qf + Hfc xc) - xf
+    double dx[NU];
+    {
+      double rhs[NU];
+      for (int i = 0; i < m; ++i) {
+        double s = -q[idx[i]];
+        for (int j = 0; j < NU; ++j)
+          if (!fr[j]) s -= H[idx[i] * NU + j] * x[j];
+        rhs[i] = s;
+      }
+      for (int i = 0; i < m; ++i) {
+        double s = rhs[i];
+        for (int r = 0; r < i; ++r) s -= Lf[i * NU + r] * rhs[r];
+        rhs[i] = s / Lf[i * NU + i];
+      }
+      for (int i = m - 1; i >= 0; --i) {
+        double s = rhs[i];
+        for (int r = i + 1; r < m; ++r) s -= Lf[r * NU + i] * rhs[r];
+        rhs[i] = s / Lf[i * NU + i];
+      }
+      for (int j = 0; j < NU; ++j) dx[j] = 0.0;
+      for (int i = 0; i < m; ++i) dx[idx[i]] = rhs[i] - x[idx[i]];
+    }
+    double fold = 0.0;
+    for (int i = 0; i < NU; ++i) {
+      double s = 0.0;
+      for (int j = 0; j < NU; ++j) s += H[i * NU + j] * x[j];
+      fold += 0.5 * x[i] * s + q[i] * x[i];
+    }
+    for (int ai = 0; ai < 10; ++ai) {
+      const double al = 1.0 / (double)(1 << ai);
+      double xn[NU];
+      for (int i = 0; i < NU; ++i) xn[i] = fmax(fmin(x[i] + al * dx[i], ub[i]), lb[i]);
+      double fnew = 0.0, gd = 0.0;
+      for (int i = 0; i < NU; ++i) {
+        double s = 0.0;
+        for (int j = 0; j < NU; ++j) s += H[i * NU + j] * xn[j];
+        fnew += 0.5 * xn[i] * s + q[i] * xn[i];
+        gd += g[i] * (x[i] - xn[i]);
+      }
+      if (fold - fnew >= th_accept * gd) {
+        for (int i = 0; i < NU; ++i) x[i] = xn[i];
+        break;
+      }
+    }
+  }
+  return true;
+}
+
+// One backward sweep with the current regularisation.  Returns false on "backward_error".
+template <class Grp, int NX, int NU>
+ASLR_HD bool backward_sweep(const Grp& g, double* sm, const SolverArgs& a, int b, const double* u_lb,
+                            const double* u_ub, bool box_limits, double xreg, double* sums /*[6]*/) {
+  typedef BwdSmem<NX, NU> SM;
+  typedef Rec<NX, NU> RC;
+  constexpr int G = Grp::G;
+  const int T = a.T;
+  const AslrOcpState& st = a.buf.state[b];
+  const bool feasible = st.is_feasible != 0;
+  const bool use_box = box_limits && feasible && (a.opts.kind == ASLR_SOLVER_BOXDDP);
+  const double* deriv = a.buf.deriv + (size_t)b * (T + 1) * RC::SIZE;
+  const double* fs = a.buf.fs + (size_t)b * (T + 1) * NX;
+  double* Vxx = sm + SM::VXX;
+  double* Vx = sm + SM::VX;
+  double* flag = sm + SM::FLAG;
+  double stop = 0, d1 = 0, d2 = 0, dgf = 0, dqf = 0;
+
+  // ---- terminal node: Vxx = Lxx + xreg I, Vx = Lx (+ Vxx fs)
+  {
+    const double* rec = deriv + (size_t)T * RC::SIZE;
+    for (int e = g.lane; e < NX * NX; e += G) Vxx[e] = rec[RC::LXX + e] + ((e / NX == e % NX) ? xreg : 0.0);
+    for (int e = g.lane; e < NX; e += G) Vx[e] = rec[RC::LX + e], sm[SM::FS + e] = fs[T * NX + e];
+    if (g.lane == 0) flag[0] = 0.0;
+    g.sync();
+    for (int e = g.lane; e < NX; e += G) {
+      double w = 0.0;
+      if (!feasible) {
+        for (int k = 0; k < NX; ++k) w += Vxx[e * NX + k] * sm[SM::FS + k];
+      }
+      sm[SM::W + e] = w;
+    }
+    g.sync();
+    for (int e = g.lane; e < NX; e += G) {
+      Vx[e] += sm[SM::W + e];
+      a.buf.Vx[((size_t)b * (T + 1) + T) * NX + e] = Vx[e];
+      a.buf.Vxxfs[((size_t)b * (T + 1) + T) * NX + e] = sm[SM::W + e];
+    }
+    if (a.buf.Vxx)
+      for (int e = g.lane; e < NX * NX; e += G) a.buf.Vxx[((size_t)b * (T + 1) + T) * NX * NX + e] = Vxx[e];
+    g.sync();
+    if (g.lane == 0 && !feasible) {
+      for (int k = 0; k < NX; ++k) dgf -= Vx[k] * sm[SM::FS + k], dqf += sm[SM::FS + k] * sm[SM::W + k];
+    }
+  }
+
+  for (int t = T - 1; t >= 0; --t) {
+    const double* rec = deriv + (size_t)t * RC::SIZE;
+    // ---- load the knot record
+    for (int e = g.lane; e < NX * NX; e += G) sm[SM::FX + e] = rec[RC::FX + e], sm[SM::QXX + e] = rec[RC::LXX + e];
+    for (int e = g.lane; e < NX * NU; e += G) sm[SM::FU + e] = rec[RC::FU + e], sm[SM::QXU + e] = rec[RC::LXU + e];
+    for (int e = g.lane; e < NU * NU; e += G) sm[SM::QUU + e] = rec[RC::LUU + e];
+    for (int e = g.lane; e < NX; e += G) sm[SM::QX + e] = rec[RC::LX + e], sm[SM::FS + e] = fs[t * NX + e];
+    for (int e = g.lane; e < NU; e += G) sm[SM::QU + e] = rec[RC::LU + e];
+    g.sync();
+    // ---- A = Fx^T Vxx', FuV = Fu^T Vxx', Qx += Fx^T Vx', Qu += Fu^T Vx'
+    for (int e = g.lane; e < NX * NX; e += G) {
+      const int i = e / NX, j = e % NX;
+      double s = 0.0;
+      for (int k = 0; k < NX; ++k) s += sm[SM::FX + k * NX + i] * Vxx[k * NX + j];
+      sm[SM::A + e] = s;
+    }
+    for (int e = g.lane; e < NU * NX; e += G) {
+      const int i = e / NX, j = e % NX;
+      double s = 0.0;
+      for (int k = 0; k < NX; ++k) s += sm[SM::FU + k * NU + i] * Vxx[k * NX + j];
+      sm[SM::FUV + e] = s;
+    }
+    for (int e = g.lane; e < NX + NU; e += G) {
+      double s = 0.0;
+      if (e < NX) {
+        for (int k = 0; k < NX; ++k) s += sm[SM::FX + k * NX + e] * Vx[k];
+        sm[SM::QX + e] += s;
+      } else {
+        for (int k = 0; k < NX; ++k) s += sm[SM::FU + k * NU + (e - NX)] * Vx[k];
+        sm[SM::QU + (e - NX)] += s;
+      }
+    }
+    g.sync();
+    // ---- Qxx += A Fx, Qxu += A Fu, Quu += FuV Fu + ureg I
+    for (int e = g.lane; e < NX * NX; e += G) {
+      const int i = e / NX, j = e % NX;
+      double s = 0.0;
+      for (int k = 0; k < NX; ++k) s += sm[SM::A + i * NX + k] * sm[SM::FX + k * NX + j];
+      sm[SM::QXX + e] += s;
+    }
+    for (int e = g.lane; e < NX * NU; e += G) {
+      const int i = e / NU, j = e % NU;
+      double s = 0.0;
+      for (int k = 0; k < NX; ++k) s += sm[SM::A + i * NX + k] * sm[SM::FU + k * NU + j];
+      sm[SM::QXU + e] += s;
+    }
+    for (int e = g.lane; e < NU * NU; e += G) {
+      const int i = e / NU, j = e % NU;
+      double s = 0.0;
+      for (int k = 0; k < NX; ++k) s += sm[SM::FUV + i * NX + k] * sm[SM::FU + k * NU + j];
+      sm[SM::QUU + e] += s + ((i == j) ? xreg : 0.0);
+    }
+    g.sync();
+    // ---- computeGains
+    if (!use_box) {
+      if (g.lane == 0) {
+        double* Lc = sm + SM::LC;
+        for (int e = 0; e < NU * NU; ++e) Lc[e] = sm[SM::QUU + e];
+        if (!cholesky<NU>(Lc)) flag[0] = 1.0;
+      }
+      g.sync();
+      if (flag[0] != 0.0) return false;
+      // K = Quu^-1 Qxu^T (one column per thread), k = Quu^-1 Qu
+      for (int e = g.lane; e < NX + 1; e += G) {
+        double col[NU];
+        for (int r = 0; r < NU; ++r) col[r] = (e < NX) ? sm[SM::QXU + e * NU + r] : sm[SM::QU + r];
+        chol_solve<NU>(sm + SM::LC, col);
+        for (int r = 0; r < NU; ++r) {
+          if (e < NX)
+            sm[SM::KG + r * NX + e] = col[r];
+          else
+            sm[SM::KF + r] = col[r];
+        }
+      }
+      g.sync();
+    } else {
+      if (g.lane == 0) {
+        double lb[NU], ub[NU], xq[NU], kinit[NU];
+        bool cl[NU];
+        const double* us = a.buf.us + ((size_t)b * T + t) * NU;
+        const double* kold = a.buf.kff + ((size_t)b * T + t) * NU;
+        for (int r = 0; r < NU; ++r) lb[r] = u_lb[r] - us[r], ub[r] = u_ub[r] - us[r], kinit[r] = kold[r];
+        if (!boxqp_solve<NU>(sm + SM::QUU, sm + SM::QU, lb, ub, kinit, xq, sm + SM::LC, cl)) flag[0] = 1.0;
+        for (int r = 0; r < NU; ++r) {
+          sm[SM::KF + r] = -xq[r];
+          if (cl[r]) sm[SM::QU + r] = 0.0;
+        }
+      }
+      g.sync();
+      if (flag[0] != 0.0) return false;
+      for (int e = g.lane; e < NU * NX; e += G) {
+        const int r = e / NX, c = e % NX;
+        double s = 0.0;
+        for (int k = 0; k < NU; ++k) s += sm[SM::LC + r * NU + k] * sm[SM::QXU + c * NU + k];
+        sm[SM::KG + e] = s;
+      }
+      g.sync();
+    }
+    // ---- Quuk = Quu k
+    for (int e = g.lane; e < NU; e += G) {
+      double s = 0.0;
+      for (int k = 0; k < NU; ++k) s += sm[SM::QUU + e * NU + k] * sm[SM::KF + k];
+      sm[SM::QUUK + e] = s;
+    }
+    g.sync();
+    // ---- Vx = Qx + K^T Quuk - 2 K^T Qu ; Vtmp = Qxx - Qxu K  (into A)
+    for (int e = g.lane; e < NX; e += G) {
+      double s1 = 0.0, s2 = 0.0;
+      for (int k = 0; k < NU; ++k) s1 += sm[SM::KG + k * NX + e] * sm[SM::QUUK + k], s2 += sm[SM::KG + k * NX + e] * sm[SM::QU + k];
+      Vx[e] = (sm[SM::QX + e] + s1) - 2.0 * s2;
+    }
+    for (int e = g.lane; e < NX * NX; e += G) {
+      const int i = e / NX, j = e % NX;
+      double s = 0.0;
+      for (int k = 0; k < NU; ++k) s += sm[SM::QXU + i * NU + k] * sm[SM::KG + k * NX + j];
+      sm[SM::A + e] = sm[SM::QXX + e] - s;
+    }
+    g.sync();
+    // ---- symmetrise + xreg
+    for (int e = g.lane; e < NX * NX; e += G) {
+      const int i = e / NX, j = e % NX;
+      Vxx[e] = 0.5 * (sm[SM::A + e] + sm[SM::A + j * NX + i]) + ((i == j) ? xreg : 0.0);
+    }
+    g.sync();
+    // ---- w = Vxx fs ; Vx += w (infeasible only) ; NaN / inf check
+    for (int e = g.lane; e < NX; e += G) {
+      double w = 0.0;
+      if (!feasible) {
+        for (int k = 0; k < NX; ++k) w += Vxx[e * NX + k] * sm[SM::FS + k];
+      }
+      sm[SM::W + e] = w;
+      Vx[e] += w;
+      double m = fabs(Vx[e]);
+      bool nan = isnan(Vx[e]);
+      for (int k = 0; k < NX; ++k) m = fmax(m, fabs(Vxx[e * NX + k])), nan = nan || isnan(Vxx[e * NX + k]);
+      if (nan || bad_value(m)) flag[0] = 1.0;
+    }
+    g.sync();
+    if (flag[0] != 0.0) return false;
+    // ---- store
+    {
+      const size_t bt = (size_t)b * T + t;
+      for (int e = g.lane; e < NU * NX; e += G) a.buf.Kgain[bt * NU * NX + e] = sm[SM::KG + e];
+      for (int e = g.lane; e < NU; e += G) {
+        a.buf.kff[bt * NU + e] = sm[SM::KF + e];
+        a.buf.Qu[bt * NU + e] = sm[SM::QU + e];
+        a.buf.Quuk[bt * NU + e] = sm[SM::QUUK + e];
+      }
+      if (a.buf.Quu)
+        for (int e = g.lane; e < NU * NU; e += G) a.buf.Quu[bt * NU * NU + e] = sm[SM::QUU + e];
+      const size_t bt1 = (size_t)b * (T + 1) + t;
+      for (int e = g.lane; e < NX; e += G) a.buf.Vx[bt1 * NX + e] = Vx[e], a.buf.Vxxfs[bt1 * NX + e] = sm[SM::W + e];
+      if (a.buf.Vxx)
+        for (int e = g.lane; e < NX * NX; e += G) a.buf.Vxx[bt1 * NX * NX + e] = Vxx[e];
+    }
+    if (g.lane == 0) {
+      for (int k = 0; k < NU; ++k) {
+        stop += sm[SM::QU + k] * sm[SM::QU + k];
+        d1 += sm[SM::QU + k] * sm[SM::KF + k];
+        d2 -= sm[SM::KF + k] * sm[SM::QUUK + k];
+      }
+      if (!feasible)
+        for (int k = 0; k < NX; ++k) dgf -= Vx[k] * sm[SM::FS + k], dqf += sm[SM::FS + k] * sm[SM::W + k];
+    }
+    g.sync();
+  }
+  if (g.lane == 0) sums[0] = stop, sums[1] = d1, sums[2] = d2, sums[3] = dgf, sums[4] = dqf;
+  return true;
+}
+
+// computeDirection() (minus calcDiff, done by K1) + expected-improvement terms for one OCP
+template <class Grp, int NX, int NU>
+ASLR_HD void backward_body(const Grp& g, double* sm, const SolverArgs& a, int b, const double* u_lb,
+                           const double* u_ub, bool box_limits, int* n_running) {
+  typedef BwdSmem<NX, NU> SM;
+  constexpr int G = Grp::G;
+  AslrOcpState& st = a.buf.state[b];
+  if (st.status != ASLR_OCP_RUNNING) return;
+  const int T = a.T;
+  // ---- cost = sum of knot costs (ShootingProblem::calcDiff), ffeas = max |gap|
+  if (st.recalc) {
+    double c = 0.0, ff = 0.0;
+    for (int t = g.lane; t <= T; t += G) c += a.buf.knot_cost[(size_t)b * (T + 1) + t];
+    for (int e = g.lane; e < (T + 1) * NX; e += G) ff = fmax(ff, fabs(a.buf.fs[(size_t)b * (T + 1) * NX + e]));
+    sm[SM::RED + g.lane] = c;
+    sm[SM::RED + 128 + g.lane] = ff;
+    g.sync();
+    if (g.lane == 0) {
+      double cs = 0.0, fm = 0.0;
+      for (int l = 0; l < G; ++l) cs += sm[SM::RED + l], fm = fmax(fm, sm[SM::RED + 128 + l]);
+      st.cost = cs;
+      st.ffeas = st.is_feasible ? 0.0 : fm;
+    }
+    g.sync();
+  }
+  double xreg = st.xreg;
+  double sums[6];
+  int retries = 0;
+  while (true) {
+    const bool ok = backward_sweep<Grp, NX, NU>(g, sm, a, b, u_lb, u_ub, box_limits, xreg, sums);
+    g.sync();
+    if (ok) break;
+    // catch (backward_error): recalcDiff = false; increaseRegularization(); give up at reg_max
+    ++retries;
+    xreg *= a.opts.reg_incfactor;
+    if (xreg > a.opts.reg_max) xreg = a.opts.reg_max;
+    if (xreg == a.opts.reg_max) {
+      if (g.lane == 0) {
+        st.xreg = xreg;
+        st.status = ASLR_OCP_REG_MAX;
+        st.n_backward_retries += retries;
+#if defined(__CUDA_ARCH__)
+        atomicSub(n_running, 1);
+#else
+        *n_running -= 1;
+#endif
+      }
+      return;
+    }
+  }
+  if (g.lane == 0) {
+    st.xreg = xreg;
+    st.n_backward_retries += retries;
+    st.stop = sums[0];
+    if (a.opts.kind == ASLR_SOLVER_FDDP) {
+      st.dg = sums[1] + sums[3];
+      st.dq = sums[2] + sums[4];
+    } else {
+      st.d1 = sums[1];
+      st.d2 = sums[2];
+    }
+  }
+}
+
+}  // namespace aslr

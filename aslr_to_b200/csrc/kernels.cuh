@@ -1,0 +1,171 @@
+// __global__ kernels and their launchers, templated on the link DOF N and the dynamics kind.
+// Explicitly instantiated per N in inst_n*.cu and dispatched from the C ABI in api.cu.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include "backward_dev.cuh"
+
+namespace aslr {
+
+struct KnotArgs {
+  int B, T;
+  const double* xs;  // [B][T+1][nx]
+  const double* us;  // [B][T][nu] or null
+  const double* K_ocp;
+  const double* mref_ocp;
+  AslrKnotOut out;
+};
+
+// ------------------------------------------------------------------------------------------ K1
+// stand-alone calc / calc+calcDiff sweep: one thread per knot (ShootingProblem.calc / calcDiff)
+template <int N, int NU, bool VSA, bool DIFF>
+__global__ void __launch_bounds__(128) knot_kernel(const __grid_constant__ DevProblem<N> P, const KnotArgs a) {
+  constexpr int NX = 4 * N;
+  typedef Rec<NX, NU> RC;
+  const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long total = (long)a.B * (a.T + 1);
+  if (g >= total) return;
+  const int b = (int)(g / (a.T + 1)), t = (int)(g % (a.T + 1));
+  const bool term = (t == a.T);
+  double x[NX], u[NU], xn[NX], cost;
+  const double* xp = a.xs + (size_t)g * NX;
+#pragma unroll
+  for (int i = 0; i < NX; ++i) x[i] = xp[i];
+  if (term || a.us == nullptr) {
+#pragma unroll
+    for (int i = 0; i < NU; ++i) u[i] = P.u_none[i];
+  } else {
+    const double* up = a.us + ((size_t)b * a.T + t) * NU;
+#pragma unroll
+    for (int i = 0; i < NU; ++i) u[i] = up[i];
+  }
+  const double* Kocp = a.K_ocp ? a.K_ocp + (size_t)b * N * N : nullptr;
+  const double* mref = a.mref_ocp ? a.mref_ocp + (size_t)b * 12 : nullptr;
+  double* rec = (DIFF && a.out.deriv) ? a.out.deriv + (size_t)g * RC::SIZE : nullptr;
+  double* xout = a.out.xout ? a.out.xout + (size_t)g * 2 * N : nullptr;
+  double* dFx = (DIFF && a.out.dFx) ? a.out.dFx + (size_t)g * 2 * N * NX : nullptr;
+  double* dFu = (DIFF && a.out.dFu) ? a.out.dFu + (size_t)g * 2 * N * NU : nullptr;
+  knot_eval<N, NU, VSA, DIFF>(P, term ? P.term : P.run, term ? P.dtT : P.dt, x, u, Kocp, mref, xn, cost, rec, xout,
+                              dFx, dFu);
+  if (a.out.cost) a.out.cost[g] = cost;
+  if (a.out.xnext && !term) {
+    double* xo = a.out.xnext + ((size_t)b * a.T + t) * NX;
+#pragma unroll
+    for (int i = 0; i < NX; ++i) xo[i] = xn[i];
+  }
+}
+
+// ------------------------------------------------------------------------------- solver kernels
+template <int N, int NU, bool VSA>
+__global__ void __launch_bounds__(128) solver_calcdiff_kernel(const __grid_constant__ DevProblem<N> P,
+                                                              const SolverArgs a) {
+  const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (long)a.B * (a.T + 1)) return;
+  calcdiff_body<N, NU, VSA>(P, a, (int)(g / (a.T + 1)), (int)(g % (a.T + 1)));
+}
+
+template <int N, int NU, bool VSA>
+__global__ void __launch_bounds__(64) rollout_kernel(const __grid_constant__ DevProblem<N> P, const SolverArgs a) {
+  const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (long)a.B * ASLR_NUM_ALPHAS) return;
+  rollout_body<N, NU, VSA>(P, a, (int)(g / ASLR_NUM_ALPHAS), (int)(g % ASLR_NUM_ALPHAS));
+}
+
+template <int NU>
+struct BoxLimits {
+  int has;
+  double lb[NU], ub[NU];
+};
+
+// warp per OCP (small nx): WARPS OCPs per CTA, each with its own shared-memory slice
+template <int NX, int NU, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS) backward_warp_kernel(const SolverArgs a, const BoxLimits<NU> lim) {
+  extern __shared__ double smem[];
+  const int w = threadIdx.x >> 5;
+  const int b = blockIdx.x * WARPS + w;
+  if (b >= a.B) return;
+  GrpWarp g{(int)(threadIdx.x & 31)};
+  backward_body<GrpWarp, NX, NU>(g, smem + (size_t)w * BwdSmem<NX, NU>::SIZE, a, b, lim.lb, lim.ub, lim.has != 0,
+                                 a.buf.counters);
+}
+
+// CTA per OCP (nx = 28)
+template <int NX, int NU, int THREADS>
+__global__ void __launch_bounds__(THREADS) backward_cta_kernel(const SolverArgs a, const BoxLimits<NU> lim) {
+  extern __shared__ double smem[];
+  const int b = blockIdx.x;
+  GrpCta<THREADS> g{(int)threadIdx.x};
+  backward_body<GrpCta<THREADS>, NX, NU>(g, smem, a, b, lim.lb, lim.ub, lim.has != 0, a.buf.counters);
+}
+
+// ------------------------------------------------------------------------------------ launchers
+struct Launchers {
+  int (*knots)(const void* P, const KnotArgs& a, int diff, cudaStream_t s);
+  int (*calcdiff)(const void* P, const SolverArgs& a, cudaStream_t s);
+  int (*backward)(const void* P, const SolverArgs& a, cudaStream_t s);
+  int (*rollout)(const void* P, const SolverArgs& a, cudaStream_t s);
+};
+
+inline int launch_status() { return cudaGetLastError() == cudaSuccess ? 0 : -2; }
+
+template <int N, bool VSA>
+struct Launch {
+  static constexpr int NX = 4 * N;
+  static constexpr int NU = VSA ? 2 * N : N;
+
+  static int knots(const void* Pv, const KnotArgs& a, int diff, cudaStream_t s) {
+    const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
+    const long total = (long)a.B * (a.T + 1);
+    if (total <= 0) return 0;
+    const int threads = 128;
+    const unsigned blocks = (unsigned)((total + threads - 1) / threads);
+    if (diff)
+      knot_kernel<N, NU, VSA, true><<<blocks, threads, 0, s>>>(P, a);
+    else
+      knot_kernel<N, NU, VSA, false><<<blocks, threads, 0, s>>>(P, a);
+    return launch_status();
+  }
+  static int calcdiff(const void* Pv, const SolverArgs& a, cudaStream_t s) {
+    const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
+    const long total = (long)a.B * (a.T + 1);
+    const int threads = 128;
+    solver_calcdiff_kernel<N, NU, VSA><<<(unsigned)((total + threads - 1) / threads), threads, 0, s>>>(P, a);
+    return launch_status();
+  }
+  static int rollout(const void* Pv, const SolverArgs& a, cudaStream_t s) {
+    const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
+    const long total = (long)a.B * ASLR_NUM_ALPHAS;
+    const int threads = 64;
+    rollout_kernel<N, NU, VSA><<<(unsigned)((total + threads - 1) / threads), threads, 0, s>>>(P, a);
+    return launch_status();
+  }
+  static int backward(const void* Pv, const SolverArgs& a, cudaStream_t s) {
+    const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
+    BoxLimits<NU> lim;
+    lim.has = P.has_limits;
+    for (int i = 0; i < NU; ++i) lim.lb[i] = P.u_lb[i], lim.ub[i] = P.u_ub[i];
+    constexpr size_t per = sizeof(double) * BwdSmem<NX, NU>::SIZE;
+    if constexpr (NX <= 12) {
+      constexpr int WARPS = 4;
+      auto k = backward_warp_kernel<NX, NU, WARPS>;
+      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(per * WARPS));
+      k<<<(a.B + WARPS - 1) / WARPS, 32 * WARPS, per * WARPS, s>>>(a, lim);
+    } else {
+      constexpr int THREADS = 128;
+      auto k = backward_cta_kernel<NX, NU, THREADS>;
+      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)per);
+      k<<<a.B, THREADS, per, s>>>(a, lim);
+    }
+    return launch_status();
+  }
+  static Launchers table() { return Launchers{&knots, &calcdiff, &backward, &rollout}; }
+};
+
+// defined in inst_n*.cu
+Launchers launchers_n2(bool vsa);
+Launchers launchers_n7(bool vsa);
+int launch_init(const SolverArgs& a, cudaStream_t s);
+int launch_accept(const SolverArgs& a, cudaStream_t s);
+
+}  // namespace aslr

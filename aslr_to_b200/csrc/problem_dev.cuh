@@ -61,7 +61,6 @@ struct Rec {
   static constexpr int SIZE = LU + NU;
 };
 
-#if !defined(__CUDA_ARCH__)
 // host-side conversion (done once in aslr_problem_create)
 template <int N>
 inline void fill_cost_sum(const AslrCostSum& src, DevCostSum<N>& dst) {
@@ -139,6 +138,5 @@ inline void fill_dev_problem(const AslrProblemDesc& s, DevProblem<N>& d) {
   fill_cost_sum<N>(s.running, d.run);
   fill_cost_sum<N>(s.terminal, d.term);
 }
-#endif
 
 }  // namespace aslr

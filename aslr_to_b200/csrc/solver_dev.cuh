@@ -1,0 +1,287 @@
+// Device-side bodies of the batched DDP / FDDP / BoxDDP solver: one function per kernel, written as
+// __host__ __device__ templates over a thread-group policy so that tests/host_harness can execute
+// the identical control flow serially on the CPU (G = 1).  Semantics follow crocoddyl `devel`
+// ~v1.9, the solver the reference calls at examples/two_dof_sea.py:69-81,
+// examples/two_dof_vsa_boxddp.py:69-81 and examples/double_pendulum.py:55,70.
+#pragma once
+
+#include "knot.cuh"
+
+namespace aslr {
+
+struct SolverArgs {
+  int B, T, iter;
+  const double* x0;
+  const double* K_ocp;
+  const double* mref_ocp;
+  AslrSolverBuffers buf;
+  AslrSolverOpts opts;
+};
+
+// crocoddyl::raiseIfNaN
+ASLR_HD bool bad_value(double v) { return isnan(v) || isinf(v) || v >= 1e30; }
+
+// ---------------------------------------------------------------------------------------------
+// solve(): initial state of one OCP (SolverDDP::solve prologue, Appendix A.1)
+// ---------------------------------------------------------------------------------------------
+ASLR_HD void init_body(const SolverArgs& a, int b) {
+  AslrOcpState& s = a.buf.state[b];
+  const double r0 = isnan(a.opts.reg_init) ? a.opts.reg_min : a.opts.reg_init;
+  s.cost = 0, s.cost_try = 0, s.stop = 0, s.xreg = r0, s.steplength = 1.0, s.dV = 0, s.dVexp = 0;
+  s.d1 = 0, s.d2 = 0, s.dg = 0, s.dq = 0, s.ffeas = 0;
+  s.iter = 0, s.status = ASLR_OCP_RUNNING, s.is_feasible = a.opts.is_feasible ? 1 : 0, s.was_feasible = 0;
+  s.recalc = 1, s.accepted = -1, s.src_slot = -1, s.n_backward_retries = 0;
+  if (b == 0) a.buf.counters[0] = a.B;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1 in solver mode: adopt the accepted trial (setCandidate), calc + calcDiff, gaps
+// (SolverDDP::calcDiff + computeDynamicFeasibility, Appendix A.2).  One thread per knot.
+// ---------------------------------------------------------------------------------------------
+template <int N, int NU, bool VSA>
+ASLR_HD void calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, int t) {
+  constexpr int NX = 4 * N;
+  typedef Rec<NX, NU> RC;
+  const AslrOcpState& s = a.buf.state[b];
+  const int T = a.T;
+  const int slot = s.src_slot;
+  const bool running = (s.status == ASLR_OCP_RUNNING) && s.recalc;
+  if (slot < 0 && !running) return;
+  double x[NX], u[NU];
+  double* xs_b = a.buf.xs + ((size_t)b * (T + 1) + t) * NX;
+  double* us_b = a.buf.us + ((size_t)b * T + (t < T ? t : 0)) * NU;
+  const double* xtry = a.buf.xs_try + (((size_t)b * ASLR_NUM_ALPHAS + (slot < 0 ? 0 : slot)) * (T + 1) + t) * NX;
+  if (slot >= 0) {
+    const double* utry = a.buf.us_try + (((size_t)b * ASLR_NUM_ALPHAS + slot) * T + (t < T ? t : 0)) * NU;
+#pragma unroll
+    for (int i = 0; i < NX; ++i) x[i] = xtry[i], xs_b[i] = x[i];
+    if (t < T) {
+#pragma unroll
+      for (int i = 0; i < NU; ++i) u[i] = utry[i], us_b[i] = u[i];
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < NX; ++i) x[i] = xs_b[i];
+    if (t < T) {
+#pragma unroll
+      for (int i = 0; i < NU; ++i) u[i] = us_b[i];
+    }
+  }
+  if (!running) return;
+  if (t == T) {
+#pragma unroll
+    for (int i = 0; i < NU; ++i) u[i] = P.u_none[i];  // terminal node: u is None
+  }
+  double xn[NX], cost;
+  const double* Kocp = a.K_ocp ? a.K_ocp + (size_t)b * N * N : nullptr;
+  const double* mref = a.mref_ocp ? a.mref_ocp + (size_t)b * 12 : nullptr;
+  double* rec = a.buf.deriv + ((size_t)b * (T + 1) + t) * RC::SIZE;
+  knot_eval<N, NU, VSA, true>(P, t == T ? P.term : P.run, t == T ? P.dtT : P.dt, x, u, Kocp, mref, xn, cost, rec,
+                              nullptr, nullptr, nullptr);
+  a.buf.knot_cost[(size_t)b * (T + 1) + t] = cost;
+  if (t < T) {
+    double* xo = a.buf.xnext + ((size_t)b * T + t) * NX;
+#pragma unroll
+    for (int i = 0; i < NX; ++i) xo[i] = xn[i];
+  }
+  // gaps: fs[0] = diff(xs[0], x0); fs[t+1] = diff(xs[t+1], xnext[t])
+  double* fs = a.buf.fs + (size_t)b * (T + 1) * NX;
+  if (!s.is_feasible) {
+    if (t < T) {
+      const double* x1 = (slot >= 0) ? xtry + NX : xs_b + NX;
+#pragma unroll
+      for (int i = 0; i < NX; ++i) fs[(t + 1) * NX + i] = xn[i] - x1[i];
+    }
+    if (t == 0) {
+#pragma unroll
+      for (int i = 0; i < NX; ++i) fs[i] = a.x0[(size_t)b * NX + i] - x[i];
+    }
+  } else if (!s.was_feasible) {
+    if (t < T) {
+#pragma unroll
+      for (int i = 0; i < NX; ++i) fs[(t + 1) * NX + i] = 0.0;
+    }
+    if (t == 0) {
+#pragma unroll
+      for (int i = 0; i < NX; ++i) fs[i] = 0.0;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3: one trial rollout = SolverDDP/FDDP/BoxDDP::forwardPass(alpha) (Appendix A.4) plus the
+// trial-dependent part of FDDP's expectedImprovement.  One thread per (OCP, alpha).
+// ---------------------------------------------------------------------------------------------
+template <int N, int NU, bool VSA>
+ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, int ai) {
+  constexpr int NX = 4 * N;
+  const AslrOcpState& s = a.buf.state[b];
+  if (s.status != ASLR_OCP_RUNNING) return;
+  const int T = a.T;
+  const int kind = a.opts.kind;
+  const double alpha = 1.0 / (double)(1 << ai);
+  const bool fddp = (kind == ASLR_SOLVER_FDDP);
+  const bool gaps = fddp && !(s.is_feasible || ai == 0);
+  const bool need_dv = fddp && !s.is_feasible;
+  const bool clamp = (kind == ASLR_SOLVER_BOXDDP) && P.has_limits;
+  const double* Kocp = a.K_ocp ? a.K_ocp + (size_t)b * N * N : nullptr;
+  const double* mref = a.mref_ocp ? a.mref_ocp + (size_t)b * 12 : nullptr;
+  const double* xs = a.buf.xs + (size_t)b * (T + 1) * NX;
+  const double* us = a.buf.us + (size_t)b * T * NU;
+  const double* fs = a.buf.fs + (size_t)b * (T + 1) * NX;
+  const double* wv = a.buf.Vxxfs + (size_t)b * (T + 1) * NX;
+  const double* Kg = a.buf.Kgain + (size_t)b * T * NU * NX;
+  const double* kf = a.buf.kff + (size_t)b * T * NU;
+  double* xt = a.buf.xs_try + ((size_t)b * ASLR_NUM_ALPHAS + ai) * (T + 1) * NX;
+  double* ut = a.buf.us_try + ((size_t)b * ASLR_NUM_ALPHAS + ai) * T * NU;
+  double* tr = a.buf.trial + ((size_t)b * ASLR_NUM_ALPHAS + ai) * 4;
+
+  double x[NX], xn[NX], u[NU];
+#pragma unroll
+  for (int i = 0; i < NX; ++i) x[i] = a.x0[(size_t)b * NX + i];
+  double cost_try = 0.0, dv = 0.0;
+  bool ok = true;
+  for (int t = 0; t < T; ++t) {
+    double dx[NX];
+#pragma unroll
+    for (int i = 0; i < NX; ++i) {
+      if (gaps) x[i] += fs[t * NX + i] * (alpha - 1.0);
+      xt[t * NX + i] = x[i];
+      dx[i] = x[i] - xs[t * NX + i];
+    }
+    if (need_dv) {
+#pragma unroll
+      for (int i = 0; i < NX; ++i) dv += wv[t * NX + i] * dx[i];
+    }
+#pragma unroll
+    for (int j = 0; j < NU; ++j) {
+      double kd = 0.0;
+#pragma unroll
+      for (int i = 0; i < NX; ++i) kd += Kg[(t * NU + j) * NX + i] * dx[i];
+      double uj = us[t * NU + j] - kf[t * NU + j] * alpha - kd;
+      if (clamp) uj = fmin(fmax(uj, P.u_lb[j]), P.u_ub[j]);
+      u[j] = uj;
+      ut[t * NU + j] = uj;
+    }
+    double c;
+    knot_eval<N, NU, VSA, false>(P, P.run, P.dt, x, u, Kocp, mref, xn, c, nullptr, nullptr, nullptr, nullptr);
+    cost_try += c;
+    double xmax = 0.0;
+    bool xnan = false;
+#pragma unroll
+    for (int i = 0; i < NX; ++i) {
+      xmax = fmax(xmax, fabs(xn[i]));
+      xnan = xnan || isnan(xn[i]);
+      x[i] = xn[i];
+    }
+    if (bad_value(cost_try) || xnan || bad_value(xmax)) {
+      ok = false;
+      break;
+    }
+  }
+  if (ok) {
+#pragma unroll
+    for (int i = 0; i < NX; ++i) {
+      if (gaps) x[i] += fs[T * NX + i] * (alpha - 1.0);
+      xt[T * NX + i] = x[i];
+      if (need_dv) dv += wv[T * NX + i] * (x[i] - xs[T * NX + i]);
+    }
+#pragma unroll
+    for (int j = 0; j < NU; ++j) u[j] = P.u_none[j];
+    double c;
+    knot_eval<N, NU, VSA, false>(P, P.term, P.dtT, x, u, Kocp, mref, xn, c, nullptr, nullptr, nullptr, nullptr);
+    cost_try += c;
+    if (bad_value(cost_try)) ok = false;
+  }
+  tr[0] = cost_try;
+  tr[1] = dv;
+  tr[2] = ok ? 1.0 : 0.0;
+  tr[3] = 0.0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K4: line-search decision + regularisation + stopping test for one OCP (the tail of
+// SolverDDP::solve / SolverFDDP::solve, Appendix A.1).  One thread per OCP.
+// ---------------------------------------------------------------------------------------------
+ASLR_HD void accept_body(const SolverArgs& a, int b, int* n_done) {
+  AslrOcpState& s = a.buf.state[b];
+  if (s.status != ASLR_OCP_RUNNING) {
+    s.src_slot = -1;  // the final candidate was adopted by the calc-diff sweep that ran before us
+    return;
+  }
+  const AslrSolverOpts& o = a.opts;
+  const bool fddp = (o.kind == ASLR_SOLVER_FDDP);
+  int accepted = -1;
+  double steplength = 1.0;
+  for (int ai = 0; ai < ASLR_NUM_ALPHAS; ++ai) {
+    const double alpha = 1.0 / (double)(1 << ai);
+    steplength = alpha;
+    const double* tr = a.buf.trial + ((size_t)b * ASLR_NUM_ALPHAS + ai) * 4;
+    if (tr[2] == 0.0) continue;  // the rollout threw (NaN / inf): try the next step length
+    s.cost_try = tr[0];
+    s.dV = s.cost - tr[0];
+    if (fddp) {
+      s.d1 = s.dg + tr[1];
+      s.d2 = s.dq - 2.0 * tr[1];
+    }
+    s.dVexp = alpha * (s.d1 + 0.5 * alpha * s.d2);
+    bool acc;
+    if (fddp) {
+      if (s.dVexp >= 0)
+        acc = (s.d1 < o.th_grad) || (s.dV > o.th_acceptstep * s.dVexp);
+      else
+        acc = s.dV > o.th_acceptnegstep * s.dVexp;
+    } else {
+      acc = (s.dVexp >= 0) && ((s.d1 < o.th_grad) || !s.is_feasible || (s.dV > o.th_acceptstep * s.dVexp));
+    }
+    if (acc) {
+      s.was_feasible = s.is_feasible;
+      s.is_feasible = fddp ? ((s.was_feasible || ai == 0) ? 1 : 0) : 1;
+      s.cost = tr[0];
+      accepted = ai;
+      break;
+    }
+  }
+  s.accepted = accepted;
+  s.recalc = (accepted >= 0) ? 1 : 0;
+  s.src_slot = accepted;
+  s.steplength = steplength;
+  if (steplength > o.th_stepdec) {
+    s.xreg /= o.reg_decfactor;
+    if (s.xreg < o.reg_min) s.xreg = o.reg_min;
+  }
+  bool finished = false;
+  if (steplength <= o.th_stepinc) {
+    s.xreg *= o.reg_incfactor;
+    if (s.xreg > o.reg_max) s.xreg = o.reg_max;
+    if (s.xreg == o.reg_max) {
+      s.status = ASLR_OCP_REG_MAX;
+      finished = true;
+    }
+  }
+  s.iter = a.iter;
+  if (!finished) {
+    if (a.buf.log) {
+      double* lg = a.buf.log + ((size_t)b * o.maxiter + a.iter) * ASLR_LOG_FIELDS;
+      lg[0] = s.cost, lg[1] = s.stop, lg[2] = s.xreg, lg[3] = s.steplength, lg[4] = s.dV, lg[5] = s.dVexp;
+      lg[6] = s.ffeas, lg[7] = (double)s.is_feasible;
+    }
+    if (s.was_feasible && s.stop < o.th_stop) {
+      s.status = ASLR_OCP_CONVERGED;
+      finished = true;
+    } else if (a.iter + 1 >= o.maxiter) {
+      s.status = ASLR_OCP_MAXITER;
+      s.iter = o.maxiter;
+      finished = true;
+    }
+  }
+  if (finished) {
+#if defined(__CUDA_ARCH__)
+    atomicSub(n_done, 1);
+#else
+    *n_done -= 1;
+#endif
+  }
+}
+
+}  // namespace aslr

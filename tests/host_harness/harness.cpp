@@ -39,3 +39,56 @@ extern "C" int hh_knot_eval(const AslrProblemDesc* desc, int terminal, int diff,
 #undef CASE
   return -1;
 }
+
+// ---------------------------------------------------------------------------------------------
+// serial emulation of aslr_solve(): the same device bodies, G = 1, all pointers on the host
+// ---------------------------------------------------------------------------------------------
+#include <vector>
+
+#include "backward_dev.cuh"
+
+template <int N, bool VSA>
+static int solve_t(const AslrProblemDesc* desc, const AslrBatch* batch, const AslrSolverOpts* opts,
+                   const AslrSolverBuffers* buf, int* iters_out) {
+  constexpr int NX = 4 * N, NU = VSA ? 2 * N : N;
+  static DevProblem<N> P;
+  fill_dev_problem<N>(*desc, P);
+  SolverArgs a;
+  a.B = batch->B, a.T = batch->T, a.iter = 0;
+  a.x0 = batch->x0, a.K_ocp = batch->K_ocp, a.mref_ocp = batch->mref_ocp;
+  a.buf = *buf;
+  a.opts = *opts;
+  std::vector<double> sm(BwdSmem<NX, NU>::SIZE);
+  for (int b = 0; b < a.B; ++b) init_body(a, b);
+  int it = 0;
+  for (it = 0; it < opts->maxiter; ++it) {
+    a.iter = it;
+    for (int b = 0; b < a.B; ++b)
+      for (int t = 0; t <= a.T; ++t) calcdiff_body<N, NU, VSA>(P, a, b, t);
+    GrpSerial g{0};
+    for (int b = 0; b < a.B; ++b)
+      backward_body<GrpSerial, NX, NU>(g, sm.data(), a, b, P.u_lb, P.u_ub, P.has_limits != 0, a.buf.counters);
+    for (int b = 0; b < a.B; ++b)
+      for (int ai = 0; ai < ASLR_NUM_ALPHAS; ++ai) rollout_body<N, NU, VSA>(P, a, b, ai);
+    for (int b = 0; b < a.B; ++b) accept_body(a, b, a.buf.counters);
+    if (a.buf.counters[0] <= 0) {
+      ++it;
+      break;
+    }
+  }
+  a.iter = it;
+  for (int b = 0; b < a.B; ++b)
+    for (int t = 0; t <= a.T; ++t) calcdiff_body<N, NU, VSA>(P, a, b, t);
+  for (int b = 0; b < a.B; ++b) accept_body(a, b, a.buf.counters);
+  if (iters_out) *iters_out = it;
+  return 0;
+}
+
+extern "C" int hh_solve(const AslrProblemDesc* desc, const AslrBatch* batch, const AslrSolverOpts* opts,
+                        const AslrSolverBuffers* buf, int* iters_out) {
+  const int n = desc->robot.n;
+  const bool vsa = desc->dyn.kind == ASLR_DYN_VSA;
+  if (n == 2) return vsa ? solve_t<2, true>(desc, batch, opts, buf, iters_out) : solve_t<2, false>(desc, batch, opts, buf, iters_out);
+  if (n == 7) return vsa ? solve_t<7, true>(desc, batch, opts, buf, iters_out) : solve_t<7, false>(desc, batch, opts, buf, iters_out);
+  return -1;
+}
