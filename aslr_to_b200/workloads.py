@@ -165,3 +165,14 @@ def to_desc(w):
     dyn = D.make_dynamics(kind, n, w["B"], w["K"], w.get("Sm"), True, w.get("u_lb"), w.get("u_ub"))
     return D.make_problem_desc(D.make_robot(rd, w["gravity"]), dyn, _abi_terms(rd, w["running"]),
                                _abi_terms(rd, w["terminal"]), w["dt"], 0.0)
+
+
+def initial_guess(w, x0, T, nu):
+    """(xs, us) arrays the examples hand to solver.solve: `empty` = ([], []) i.e. state.zero() / zeros
+    (examples/two_dof_vsa_boxddp.py:81); otherwise xs = [x0] * (T + 1) and us = quasiStatic(x0), which is
+    zero for every example because q_l = q_m at x0."""
+    x0 = np.atleast_2d(np.asarray(x0, float))
+    B, nx = x0.shape
+    if w["init"] == "empty":
+        return np.zeros((B, T + 1, nx)), np.zeros((B, T, nu))
+    return np.repeat(x0[:, None, :], T + 1, axis=1), np.zeros((B, T, nu))

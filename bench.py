@@ -1,0 +1,313 @@
+#!/usr/bin/env python3
+"""bench.py -- headline benchmark of the batched DDP hot path (BASELINE.json).
+
+Metric: batched FDDP OCP-iterations/s (sum over OCPs of solver iterations / time) on BASELINE.json
+configs[3]: 4096 independent 2-DOF SEA reaching OCPs (T = 100, random initial posture / joint
+stiffness, default_rng(20240001)) solved to convergence (th_stop 1e-7, maxiter 100).  A "step" is one
+complete solve of the batch from the same initial guess.  Also reported: fused calc+calcDiff knots/s
+(the metric's second half) with its HBM roofline, an end-to-end number through the public API with
+host buffers, and the CPU oracle timed on the host cores.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]          our CUDA path
+  python bench.py --impl reference ...                          the reference-equivalent CPU path
+
+Multi-GPU (weak scaling): one process per GPU under torchrun, every rank solves its own 4096-OCP batch
+(seed + rank); there is no per-iteration collective, only a final NCCL all-gather of costs, iteration
+counts and trajectories (inside the timed region).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "batched_fddp_ocp_iters_per_s"
+UNIT = "OCP-iterations/s"
+B_PER_GPU = 4096
+SEED = 20240001
+ALGO_BYTES_PER_KNOT = 1544  # 2-DOF SEA, read x,u; write xnext,cost,Fx,Fu,Lx,Lu,Lxx,Lxu,Luu
+
+
+def workload_config(n_gpus):
+    return {"workload": "4096 x 2-DOF SEA FDDP reaching OCPs per GPU (BASELINE.json configs[3]), T=100, "
+                        "th_stop=1e-7, maxiter=100, solved to convergence",
+            "ocps_per_gpu": B_PER_GPU, "T": 100, "nx": 8, "nu": 2, "solver": "fddp",
+            "parallelism": "independent OCPs sharded over %d GPU(s), no per-iteration collective" % n_gpus,
+            "l2": "per-iteration working set (derivative records 576 MB + trial trajectories 331 MB per GPU) "
+                  "exceeds the 126 MB L2, no explicit flush"}
+
+
+# ------------------------------------------------------------------------------------ clocks
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])), mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------ CPU baselines
+def _cpu_worker(args):
+    b, seed = args
+    import oracle_build as ob
+    from aslr_to_b200 import workloads as W
+    w = W.sea_batch(B_PER_GPU, seed=seed)
+    t0 = time.perf_counter()
+    solver, log = ob.solve(w, b, "port")
+    return len(log.costs), time.perf_counter() - t0
+
+
+def cpu_oracle_rate(n_ocps, procs, seed=SEED):
+    """OCP-iterations/s of the NumPy oracle (reference-equivalent CPU path) on `procs` host cores."""
+    import multiprocessing as mp
+    jobs = [(b, seed) for b in range(n_ocps)]
+    t0 = time.perf_counter()
+    if procs == 1:
+        res = [_cpu_worker(j) for j in jobs]
+    else:
+        with mp.get_context("spawn").Pool(procs) as pool:
+            res = pool.map(_cpu_worker, jobs)
+    wall = time.perf_counter() - t0
+    iters = sum(r[0] for r in res)
+    return iters / wall, iters, wall
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU algorithm (oracle port: the reference's model maths on the
+    NumPy restatement of crocoddyl/pinocchio -- the originals cannot be built here) on all
+    host cores; each step is a bounded sample (one OCP per core) of the same workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    for _ in range(args.warmup if args.warmup < 1 else 1):
+        cpu_oracle_rate(cores, cores)
+    t_total, it_total = 0.0, 0
+    for _ in range(args.steps):
+        rate, iters, wall = cpu_oracle_rate(cores, cores)
+        t_total += wall
+        it_total += iters
+    value = it_total / t_total
+    sample = "%d OCPs (one per core) of the 4096-OCP batch per step, full FDDP solve each" % cores
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * t_total / max(args.steps, 1),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# -------------------------------------------------------------------------------- our CUDA arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from aslr_to_b200 import _abi as A, batched as BT, workloads as W
+    initial_guess_arrays = W.initial_guess
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the product path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    w = W.sea_batch(B_PER_GPU, seed=SEED + rank)
+    B, T, nx, nu = B_PER_GPU, w["T"], 8, 2
+    prob = BT.BatchedShootingProblem(W.to_desc(w), w["x0"], T, K_ocp=w["K_ocp"], device=dev)
+    solver = BT.BatchedSolver(prob, A.SOLVER_FDDP, maxiter=w["maxiter"], th_stop=w["th_stop"], store_vxx=False,
+                              store_quu=False, store_log=False)
+    xs0_h, us0_h = initial_guess_arrays(w, np.asarray(w["x0"]), T, nu)
+    # pinned host buffers = what a caller of the public API holds
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    h_x0, h_K, h_xs0, h_us0 = pin(w["x0"]), pin(np.asarray(w["K_ocp"]).reshape(B, 4)), pin(xs0_h), pin(us0_h)
+    d_xs0, d_us0 = h_xs0.to(dev), h_us0.to(dev)
+    h_xs = torch.empty((B, T + 1, nx), dtype=torch.float64).pin_memory()
+    h_us = torch.empty((B, T, nu), dtype=torch.float64).pin_memory()
+    h_state = torch.empty((B, A.OCP_STATE_DOUBLES), dtype=torch.float64).pin_memory()
+    gather = None
+    if world > 1:
+        gather = {k: torch.empty((world,) + tuple(solver.t[k].shape), dtype=torch.float64, device=dev)
+                  for k in ("xs", "us", "state")}
+
+    def step_device():
+        solver.t["xs"].copy_(d_xs0)
+        solver.t["us"].copy_(d_us0)
+        solver.solve(set_candidate=False)
+        if world > 1:  # the only collective of the path: final gather of costs / iterations / trajectories
+            for k in ("xs", "us", "state"):
+                dist.all_gather_into_tensor(gather[k], solver.t[k])
+
+    def step_e2e():
+        prob.x0.copy_(h_x0, non_blocking=True)
+        prob.K_ocp.copy_(h_K, non_blocking=True)
+        solver.t["xs"].copy_(h_xs0, non_blocking=True)
+        solver.t["us"].copy_(h_us0, non_blocking=True)
+        solver.solve(set_candidate=False)
+        h_xs.copy_(solver.t["xs"], non_blocking=True)
+        h_us.copy_(solver.t["us"], non_blocking=True)
+        h_state.copy_(solver.t["state"], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    torch.cuda.synchronize()
+    st = solver.states()
+    iters_per_solve = int(np.sum(st["iter"] + (st["status"] == A.OCP_CONVERGED)))
+    n_conv = int(np.sum(st["status"] == A.OCP_CONVERGED))
+    launches_per_step = int(solver.result.kernel_launches)
+    tot = torch.tensor([float(iters_per_solve)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot)
+    total_iters = float(tot.item())
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms = timed(step_device, args.steps)
+    ms_e2e = timed(step_e2e, args.steps)
+    value = total_iters * args.steps / (ms * 1e-3)
+    e2e_value = total_iters * args.steps / (ms_e2e * 1e-3)
+
+    # ---- dominant-kernel roofline: the fused calc+calcDiff sweep over the batch's B*(T+1) knots
+    xs_sol, us_sol = solver.t["xs"].clone(), solver.t["us"].clone()
+    out = A.KnotOut()
+    out.xnext, out.cost, out.deriv = solver.t["xnext"].data_ptr(), solver.t["knot_cost"].data_ptr(), \
+        solver.t["deriv"].data_ptr()
+    bs = prob.batch_struct()
+    import ctypes as C
+    stream = prob._stream()
+
+    def calcdiff_sweep():
+        A.check(prob.lib.aslr_calc_diff(prob.handle, C.byref(bs), xs_sol.data_ptr(), us_sol.data_ptr(), C.byref(out),
+                                        stream))
+    for _ in range(3):
+        calcdiff_sweep()
+    reps = 20
+    ms_k1 = timed(lambda: calcdiff_sweep(), reps) / reps
+    clocks = sampler.stop() if rank == 0 else None
+    knots = B * (T + 1)
+    knots_per_s = knots * world / (ms_k1 * 1e-3)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = ALGO_BYTES_PER_KNOT * knots / (ms_k1 * 1e-3) / 1e9
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(world),
+            "ocp_iters_per_solve_all_gpus": total_iters, "converged_rank0": n_conv,
+            "calcdiff_knots_per_s": knots_per_s, "calcdiff_ms": ms_k1,
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+                    "h2d_bytes_per_step": int(h_x0.nbytes + h_K.nbytes + h_xs0.nbytes + h_us0.nbytes),
+                    "d2h_bytes_per_step": int(h_xs.nbytes + h_us.nbytes + h_state.nbytes)},
+            "gpu_launches": launches_per_step * args.steps,
+            "roofline": {"kernel": "knot_kernel<2,2,SEA,DIFF> (fused calc+calcDiff, %d knots)" % knots,
+                         "bound": "hbm", "achieved": achieved, "peak": peak,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": None},
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu:
+            rate, iters, wall = cpu_oracle_rate(args.cpu_ocps, 1)
+            line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": 1, "kind": "port",
+                                    "sample": "%d OCPs of the same batch, full FDDP solve each (%d iterations, %.1f s)"
+                                              % (args.cpu_ocps, iters, wall)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-ocps", type=int, default=2, help="OCPs in the bounded CPU-oracle sample")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -69,6 +69,10 @@ def solver_trace(solver, log):
                 cost=np.array(solver.cost), stop=np.array(solver.stop))
 
 
+def _have(path):
+    return os.path.isfile(path) and "--force" not in sys.argv
+
+
 def main():
     if not ob.refenv.have_reference():
         raise SystemExit("/root/reference is not available: golden vectors can only be made in the build container")
@@ -78,12 +82,16 @@ def main():
                running=[t for t in c7["running"] if t["kind"] != "control"] +
                [dict(name="uReg", kind="control", weight=1e-2, ref=np.zeros(14), act=np.ones(14), frame=None)])
     for w, ns in [(s, 16) for s in singles] + [(c7, 6), (c7v, 6)]:
+        if _have(os.path.join(HERE, "knots_%s.npz" % w["name"].split("_batch")[0])):
+            continue
         xs, us = knot_samples(w, ns, 1234)
         res = eval_knots(ob.reference_models(w, 0), xs, us)
         np.savez_compressed(os.path.join(HERE, "knots_%s.npz" % w["name"].split("_batch")[0]), xs=xs, us=us, **res)
         print("knots", w["name"], ns)
     for w in singles:
         t0 = time.time()
+        if _have(os.path.join(HERE, "solve_%s.npz" % w["name"])):
+            continue
         solver, log = ob.solve(w, 0, "reference")
         np.savez_compressed(os.path.join(HERE, "solve_%s.npz" % w["name"]), **solver_trace(solver, log))
         print("solve", w["name"], "iters", solver.iter, "converged", solver.converged, "cost", solver.cost,
@@ -93,6 +101,8 @@ def main():
         wb = W.sea_batch(4096, solver=solver_name)
         for b in (0, 1):
             t0 = time.time()
+            if _have(os.path.join(HERE, "solve_sea_batch_%s_b%d.npz" % (solver_name, b))):
+                continue
             solver, log = ob.solve(wb, b, "reference")
             np.savez_compressed(os.path.join(HERE, "solve_sea_batch_%s_b%d.npz" % (solver_name, b)),
                                 **solver_trace(solver, log))

@@ -1,0 +1,179 @@
+"""GPU tier (`-m gpu`, run on the B200 box): the CUDA kernels, called through the C ABI, against
+  * the committed golden vectors (generated from the reference's own classes, tests/golden/make_golden.py),
+  * the oracle port on the same seeded inputs (sizes the oracle finishes in seconds),
+  * size-independent properties at BASELINE.json's full batch size.
+Tolerance: 1e-9 relative on cost, gradients and gains with identical iteration counts
+(BASELINE.json north_star), written as util.RTOL."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_build as ob
+from aslr_to_b200 import _abi as A
+from aslr_to_b200 import workloads as W
+from test_oracle_pinning import SINGLES, all_knot_workloads
+from util import GOLDEN, RTOL, compare_solver_trace, golden, initial_guess_arrays, rel_err
+
+pytestmark = pytest.mark.gpu
+
+KNOT_FIELDS = ("xnext", "cost", "xout", "dFx", "dFu", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu")
+
+
+@pytest.fixture(scope="module")
+def BT(built_library):
+    import torch
+    assert torch.cuda.is_available(), "the gpu tier needs a CUDA device"
+    from aslr_to_b200 import batched
+    assert batched.A.load_library().aslr_device_count() >= 1
+    return batched
+
+
+def gpu_solve(BT, w, ocps=None, maxiter=None, T=None):
+    desc = W.to_desc(w)
+    x0 = np.atleast_2d(np.asarray(w["x0"], float))
+    K, mref = w.get("K_ocp"), w.get("mref_ocp")
+    if ocps is not None:
+        x0 = x0[ocps]
+        K = None if K is None else np.asarray(K)[ocps]
+        mref = None if mref is None else np.asarray(mref)[ocps]
+    T = w["T"] if T is None else T
+    prob = BT.BatchedShootingProblem(desc, x0, T, K_ocp=K, mref_ocp=mref)
+    maxiter = w["maxiter"] if maxiter is None else maxiter
+    solver = BT.BatchedSolver(prob, W.SOLVER_KIND[w["solver"]], maxiter=maxiter, th_stop=w["th_stop"])
+    xs, us = initial_guess_arrays(w, x0, T, prob.nu)
+    solver.solve(xs, us)
+    res = dict((k, v.cpu().numpy()) for k, v in solver.t.items())
+    res["log"] = solver.logs()
+    res["states"] = solver.states()
+    res["result"] = solver.result
+    return res
+
+
+@pytest.mark.parametrize("name", ["double_pendulum", "two_dof_sea", "two_dof_vsa_boxddp", "two_dof_vsa_modified",
+                                  "chain7", "chain7_vsa"])
+def test_calc_and_calcdiff_kernels_match_golden(BT, name):
+    """One knot per (x, u) sample: B = nsamples, T = 1 so that knot 0 is a running node and knot 1 the
+    terminal node evaluated at the same x with u = None."""
+    w = all_knot_workloads()[name]
+    g = golden("knots_" + name)
+    ns = g["xs"].shape[0]
+    mref = None if w.get("mref_ocp") is None else np.repeat(w["mref_ocp"][:1], ns, axis=0)
+    prob = BT.BatchedShootingProblem(W.to_desc(w), g["xs"], 1, mref_ocp=mref)
+    xs = np.repeat(g["xs"][:, None, :], 2, axis=1)
+    us = g["us"][:, None, :]
+    out = prob.calc_diff(xs, us, want=("xnext", "cost", "deriv", "xout", "dFx", "dFu"))
+    out = dict((k, v.cpu().numpy()) for k, v in out.items())
+    out.update(prob.split_record(out["deriv"]))
+    co = dict((k, v.cpu().numpy()) for k, v in prob.calc(xs, us, want=("xnext", "cost", "xout")).items())
+    for tag, t in (("run_", 0), ("term_", 1)):
+        for k in KNOT_FIELDS:
+            ours = out[k][:, 0] if (k == "xnext") else out[k][:, t]
+            if k == "xnext" and t == 1:
+                continue  # the terminal node has no successor
+            assert rel_err(ours, g[tag + k]) < RTOL, (name, tag, k)
+    # calc-only kernel (the one the rollout uses) agrees with the fused kernel
+    assert rel_err(co["xnext"], out["xnext"]) < 1e-13
+    assert rel_err(co["cost"], out["cost"]) < 1e-13
+    assert rel_err(co["xout"], out["xout"]) < 1e-13
+
+
+@pytest.mark.parametrize("name", ["two_dof_sea", "double_pendulum", "two_dof_vsa_boxddp", "two_dof_vsa_modified"])
+def test_example_solves_match_golden_traces(BT, name):
+    path = os.path.join(GOLDEN, "solve_%s.npz" % name)
+    if not os.path.isfile(path):
+        pytest.skip("golden trace %s not generated" % name)
+    res = gpu_solve(BT, SINGLES[name]())
+    if name == "double_pendulum":
+        # chaotic, non-converging example: decisions identical, values drift (parity notes)
+        compare_solver_trace(res, 0, golden("solve_" + name), n_tight=2, loose=5e-2, check_gains=False)
+    else:
+        compare_solver_trace(res, 0, golden("solve_" + name))
+
+
+@pytest.mark.parametrize("solver", ["fddp", "ddp"])
+def test_batch_members_match_golden_and_are_batch_invariant(BT, solver):
+    """OCPs 0 and 1 of the 4096 batch against the reference traces; and solving them inside a batch of 64
+    gives bit-identical results to solving them alone (no cross-OCP coupling)."""
+    if not os.path.isfile(os.path.join(GOLDEN, "solve_sea_batch_%s_b1.npz" % solver)):
+        pytest.skip("golden trace not generated")
+    w = W.sea_batch(4096, solver=solver)
+    small = gpu_solve(BT, w, ocps=[0, 1])
+    for b in (0, 1):
+        compare_solver_trace(small, b, golden("solve_sea_batch_%s_b%d" % (solver, b)))
+    big = gpu_solve(BT, w, ocps=list(range(64)))
+    for k in ("xs", "us", "Kgain", "kff"):
+        assert np.array_equal(big[k][:2], small[k][:2]), k
+    assert np.array_equal(big["states"]["iter"][:2], small["states"]["iter"][:2])
+
+
+def test_oracle_port_on_seeded_batch_members(BT):
+    """Fresh seeded inputs (not in the golden set): three OCPs of a seed-7 batch, T = 30, against the
+    oracle port's FDDP."""
+    w = W.sea_batch(16, seed=7)
+    w["maxiter"] = 30
+    res = gpu_solve(BT, w, T=30)
+    for b in (2, 9, 15):
+        solver, log = ob.solve(w, b, "port", T=30)
+        st = res["states"]
+        it = int(st["iter"][b]) + (1 if st["status"][b] == A.OCP_CONVERGED else 0)
+        assert it == len(log.costs)
+        assert rel_err(res["log"][b][:it, 0], log.costs) < RTOL
+        assert rel_err(res["log"][b][:it, 3], log.steps) == 0
+        assert rel_err(res["xs"][b], np.array(solver.xs)) < RTOL
+        assert rel_err(res["us"][b], np.array(solver.us)) < RTOL
+        assert rel_err(res["Kgain"][b], np.array(solver.K)) < RTOL
+        assert rel_err(res["kff"][b], np.array(solver.k)) < RTOL
+
+
+def test_chain7_solve_matches_oracle_port(BT):
+    """nx = 28 path (CTA-per-OCP backward pass): 2 OCPs, T = 12, 4 iterations."""
+    w = W.chain7_batch(B=2, T=12)
+    w["maxiter"] = 4
+    res = gpu_solve(BT, w)
+    for b in (0, 1):
+        solver, log = ob.solve(w, b, "port")
+        it = len(log.costs)
+        assert rel_err(res["log"][b][:it, 0], log.costs) < RTOL
+        assert rel_err(res["log"][b][:it, 3], log.steps) == 0
+        assert rel_err(res["xs"][b], np.array(solver.xs)) < RTOL
+        assert rel_err(res["Kgain"][b], np.array(solver.K)) < 1e-8
+        assert rel_err(res["Vxx"][b], np.array(solver.Vxx)) < RTOL
+
+
+def test_full_batch_properties(BT):
+    """BASELINE.json configs[3] at full size (4096 OCPs, T = 100): every OCP converges; the converged
+    trajectories are dynamically feasible (re-rolling the controls out with the calc kernel reproduces
+    xs); the summed knot costs equal the solver's cost; a second solve is bit-identical."""
+    import torch
+    w = W.sea_batch(4096)
+    desc = W.to_desc(w)
+    prob = BT.BatchedShootingProblem(desc, w["x0"], w["T"], K_ocp=w["K_ocp"])
+    solver = BT.BatchedSolver(prob, A.SOLVER_FDDP, maxiter=100, th_stop=1e-7, store_vxx=False, store_quu=False)
+    xs, us = initial_guess_arrays(w, np.asarray(w["x0"]), w["T"], 2)
+    solver.solve(xs, us)
+    st = solver.states()
+    assert (st["status"] == A.OCP_CONVERGED).all()
+    assert np.isfinite(st["cost"]).all() and (st["stop"] < 1e-7).all()
+    xs_sol, us_sol = solver.get("xs"), solver.get("us")
+    assert torch.equal(xs_sol[:, 0], prob.x0)
+    out = prob.calc(xs_sol, us_sol)
+    gap = (out["xnext"] - xs_sol[:, 1:]).abs().max().item()
+    assert gap < 1e-12, gap
+    assert abs(out["cost"].sum(dim=1).cpu().numpy() - st["cost"]).max() < 1e-9 * np.abs(st["cost"]).max()
+    # determinism: a second solve of the same batch is bit-identical
+    xs1, iters = xs_sol.clone(), st["iter"].copy()
+    solver.solve(xs, us)
+    assert np.array_equal(solver.states()["iter"], iters) and torch.equal(solver.get("xs"), xs1)
+    assert iters.max() < 100
+
+
+def test_missing_device_pointers_are_rejected(BT):
+    w = W.two_dof_sea()
+    prob = BT.BatchedShootingProblem(W.to_desc(w), w["x0"][None, :], 5)
+    buf = A.SolverBuffers()
+    import ctypes as C
+    b = prob.batch_struct()
+    o = BT.make_opts(A.SOLVER_FDDP, 3)
+    rc = prob.lib.aslr_solve(prob.handle, C.byref(b), C.byref(o), C.byref(buf), None, None)
+    assert rc == -1 and b"null" in prob.lib.aslr_last_error()

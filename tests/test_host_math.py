@@ -1,0 +1,81 @@
+"""CPU tier: the product's __host__ __device__ arithmetic (aslr_to_b200/csrc/*.cuh), compiled with g++
+by tests/host_harness, against the golden vectors of the reference and the oracle solver traces.
+The kernels proper are exercised by the `-m gpu` tests; this tier catches arithmetic and
+control-flow errors without a GPU.  Nothing here is a product path."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_build as ob
+from aslr_to_b200 import workloads as W
+from test_oracle_pinning import SINGLES, all_knot_workloads
+from util import GOLDEN, RTOL, compare_solver_trace, golden, host_knot, host_solve, rel_err
+
+KNOT_FIELDS = ("xnext", "cost", "xout", "dFx", "dFu", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu")
+
+
+@pytest.mark.parametrize("name", ["double_pendulum", "two_dof_sea", "two_dof_vsa_boxddp", "two_dof_vsa_modified",
+                                  "chain7", "chain7_vsa"])
+def test_knot_arithmetic_matches_golden(hostmath, name):
+    w = all_knot_workloads()[name]
+    g = golden("knots_" + name)
+    desc = W.to_desc(w)
+    mref = None if w.get("mref_ocp") is None else w["mref_ocp"][0]
+    worst = 0.0
+    for i, (x, u) in enumerate(zip(g["xs"], g["us"])):
+        for tag, term in (("run_", False), ("term_", True)):
+            out = host_knot(hostmath, desc, x, None if term else u, terminal=term, mref=mref)
+            for k in KNOT_FIELDS:
+                e = rel_err(out[k], g[tag + k][i])
+                worst = max(worst, e)
+                assert e < RTOL, (name, tag, k, i, e)
+    assert worst < 1e-11  # in practice ~1e-13
+
+
+def test_calc_only_path_equals_calc_diff_path(hostmath):
+    """The rollout uses the DIFF = false instantiation: same xnext / cost as the fused one."""
+    w = W.two_dof_vsa_modified()
+    desc = W.to_desc(w)
+    g = golden("knots_two_dof_vsa_modified")
+    for x, u in zip(g["xs"], g["us"]):
+        a = host_knot(hostmath, desc, x, u, diff=True)
+        b = host_knot(hostmath, desc, x, u, diff=False)
+        assert rel_err(a["xnext"], b["xnext"]) < 1e-13 and abs(a["cost"] - b["cost"]) < 1e-12 * max(1, abs(a["cost"]))
+
+
+def test_per_ocp_stiffness_and_target_override(hostmath):
+    w = W.sea_batch(8)
+    desc = W.to_desc(w)
+    run, term, x0 = ob.port_models(w, 3)
+    d = run.createData()
+    u = np.array([0.3, -0.2])
+    x = x0 + 0.1
+    run.calc(d, x, u), run.calcDiff(d, x, u)
+    out = host_knot(hostmath, desc, x, u, Kocp=w["K_ocp"][3])
+    for k in ("xnext", "Fx", "Fu", "Lx", "Lxx"):
+        assert rel_err(out[k], getattr(d, k)) < 1e-12
+
+
+@pytest.mark.parametrize("name", ["two_dof_sea", "double_pendulum", "two_dof_vsa_boxddp", "two_dof_vsa_modified"])
+def test_solver_control_flow_matches_golden_trace(hostmath, name):
+    """Same iteration count, step lengths, regularisation; cost / gains / trajectory within 1e-9."""
+    path = os.path.join(GOLDEN, "solve_%s.npz" % name)
+    if not os.path.isfile(path):
+        pytest.skip("golden trace %s not generated" % name)
+    w = SINGLES[name]()
+    res = host_solve(hostmath, w)
+    if name == "double_pendulum":
+        compare_solver_trace(res, 0, golden("solve_" + name), n_tight=2, loose=5e-2, check_gains=False)
+    else:
+        compare_solver_trace(res, 0, golden("solve_" + name))
+
+
+@pytest.mark.parametrize("solver", ["fddp", "ddp"])
+def test_batch_members_match_golden_trace(hostmath, solver):
+    if not os.path.isfile(os.path.join(GOLDEN, "solve_sea_batch_%s_b1.npz" % solver)):
+        pytest.skip("golden trace not generated")
+    w = W.sea_batch(4096, solver=solver)
+    res = host_solve(hostmath, w, ocps=[0, 1])
+    for b in (0, 1):
+        compare_solver_trace(res, b, golden("solve_sea_batch_%s_b%d" % (solver, b)))

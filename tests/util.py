@@ -72,13 +72,7 @@ def default_opts(kind, maxiter, th_stop=None):
     return o
 
 
-def initial_guess_arrays(w, x0, T, nu):
-    """(xs, us) arrays for the batched solvers, matching oracle_build.initial_guess.  For the examples
-    that start from quasiStatic(x0) the result is u = 0 because q_l = q_m at x0."""
-    B, nx = x0.shape
-    if w["init"] == "empty":
-        return np.zeros((B, T + 1, nx)), np.zeros((B, T, nu))
-    return np.repeat(x0[:, None, :], T + 1, axis=1), np.zeros((B, T, nu))
+initial_guess_arrays = W.initial_guess
 
 
 def host_solve(hostmath, w, ocps=None, maxiter=None, T=None):
@@ -120,16 +114,23 @@ def host_solve(hostmath, w, ocps=None, maxiter=None, T=None):
     return arr
 
 
-def compare_solver_trace(res, b, gold, rtol=RTOL, check_gains=True):
-    """res: arrays of a batched solve (host emulation or GPU); gold: golden npz of the oracle solver."""
+def compare_solver_trace(res, b, gold, rtol=RTOL, check_gains=True, n_tight=None, loose=None):
+    """res: arrays of a batched solve (host emulation or GPU); gold: golden npz of the oracle solver.
+    Iteration counts, accepted step lengths and regularisation must be identical; values within rtol.
+    n_tight/loose: for the chaotic double-pendulum example only the first n_tight iterations are held to
+    rtol and everything after (including the final trajectory and gains) to `loose`."""
     st = res["states"]
     n_it = len(gold["costs"])
     it_ours = int(st["iter"][b]) + (1 if st["status"][b] == A.OCP_CONVERGED else 0)
     assert bool(gold["converged"]) == (st["status"][b] == A.OCP_CONVERGED), (st["status"][b], gold["converged"])
     assert it_ours == n_it, "iteration count differs: ours %d, oracle %d" % (it_ours, n_it)
     lg = res["log"][b][:n_it]
+    assert rel_err(lg[:, 3], gold["steps"]) == 0, "accepted step lengths differ"
+    assert rel_err(lg[:, 2], gold["x_regs"]) == 0, "regularisation sequence differs"
+    if n_tight is not None:
+        assert rel_err(lg[:n_tight, 0], gold["costs"][:n_tight]) <= rtol
+        rtol = loose
     errs = dict(cost=rel_err(lg[:, 0], gold["costs"]), stop=rel_err(lg[:, 1], gold["stops"]),
-                xreg=rel_err(lg[:, 2], gold["x_regs"]), step=rel_err(lg[:, 3], gold["steps"]),
                 xs=rel_err(res["xs"][b], gold["xs"]), us=rel_err(res["us"][b], gold["us"]))
     if check_gains:
         errs.update(K=rel_err(res["Kgain"][b], gold["K"]), k=rel_err(res["kff"][b], gold["k"]),
