@@ -219,6 +219,13 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    if args.profile:  # for ncu: one warm-up solve, one profiled solve, nothing else
+        step_device()
+        torch.cuda.synchronize()
+        step_device()
+        torch.cuda.synchronize()
+        print(json.dumps({"profile": True, "kernel_launches_per_solve": int(solver.result.kernel_launches)}))
+        return
     for _ in range(max(args.warmup, 3)):
         step_device()
     torch.cuda.synchronize()
@@ -302,6 +309,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-ocps", type=int, default=2, help="OCPs in the bounded CPU-oracle sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--profile", action="store_true", help="two solves only (for ncu launch lists)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

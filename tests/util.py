@@ -114,11 +114,14 @@ def host_solve(hostmath, w, ocps=None, maxiter=None, T=None):
     return arr
 
 
-def compare_solver_trace(res, b, gold, rtol=RTOL, check_gains=True, n_tight=None, loose=None):
+def compare_solver_trace(res, b, gold, rtol=RTOL, check_gains=True, n_tight=None, loose=None, trace_rtol=None):
     """res: arrays of a batched solve (host emulation or GPU); gold: golden npz of the oracle solver.
     Iteration counts, accepted step lengths and regularisation must be identical; values within rtol.
     n_tight/loose: for the chaotic double-pendulum example only the first n_tight iterations are held to
-    rtol and everything after (including the final trajectory and gains) to `loose`."""
+    rtol and everything after (including the final trajectory and gains) to `loose`.
+    trace_rtol: tolerance of the per-iteration cost / stop logs when it differs from rtol (solves of several
+    hundred iterations amplify rounding differences in the intermediate iterates; the final solution and
+    gains are still held to rtol)."""
     st = res["states"]
     n_it = len(gold["costs"])
     it_ours = int(st["iter"][b]) + (1 if st["status"][b] == A.OCP_CONVERGED else 0)
@@ -130,8 +133,11 @@ def compare_solver_trace(res, b, gold, rtol=RTOL, check_gains=True, n_tight=None
     if n_tight is not None:
         assert rel_err(lg[:n_tight, 0], gold["costs"][:n_tight]) <= rtol
         rtol = loose
-    errs = dict(cost=rel_err(lg[:, 0], gold["costs"]), stop=rel_err(lg[:, 1], gold["stops"]),
-                xs=rel_err(res["xs"][b], gold["xs"]), us=rel_err(res["us"][b], gold["us"]))
+    trace_rtol = rtol if trace_rtol is None else trace_rtol
+    assert rel_err(lg[:, 0], gold["costs"]) <= trace_rtol, rel_err(lg[:, 0], gold["costs"])
+    assert rel_err(lg[:, 1], gold["stops"]) <= trace_rtol, rel_err(lg[:, 1], gold["stops"])
+    errs = dict(cost=rel_err(lg[-1:, 0], gold["costs"][-1:]), xs=rel_err(res["xs"][b], gold["xs"]),
+                us=rel_err(res["us"][b], gold["us"]))
     if check_gains:
         errs.update(K=rel_err(res["Kgain"][b], gold["K"]), k=rel_err(res["kff"][b], gold["k"]),
                     Vx=rel_err(res["Vx"][b], gold["Vx"]), Vxx=rel_err(res["Vxx"][b], gold["Vxx"]),
