@@ -93,7 +93,7 @@ def chain7():
         p = [0, 0, 0.0] if i == 0 else [0.01 * (i % 3), 0, 0.3]
         m = masses[i]
         com = [0.02, -0.01 * (1 + i % 2), 0.15]
-        a, b, c = m * 0.3 ** 2 / 12, m * 0.3 ** 2 / 12 * 0.9, m * 0.03 ** 2
+        a, b, c = m * 0.3 ** 2 / 12, m * 0.3 ** 2 / 12 * 0.9, m * 0.09 ** 2
         inertia = np.array([[a, 0.02 * a, 0.01 * a], [0.02 * a, b, -0.015 * a], [0.01 * a, -0.015 * a, c]])
         j.append(joint("joint%d" % (i + 1), R, p, axis, m, com, inertia, -2.5, 2.5))
     f = [frame("universe", -1, np.eye(3), [0, 0, 0])]
