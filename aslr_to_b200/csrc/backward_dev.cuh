@@ -42,7 +42,8 @@ struct BwdSmem {
   static constexpr int KG = FUV + NU * NX;
   static constexpr int QUU = KG + NU * NX;
   static constexpr int LC = QUU + NU * NU;  // Cholesky factor of Quu / Quu_inv for the box QP
-  static constexpr int VX = LC + NU * NU;
+  static constexpr int LINV = LC + NU * NU;  // reciprocal diagonal of the Cholesky factor
+  static constexpr int VX = LINV + NU + (NU & 1);
   static constexpr int QX = VX + NX;
   static constexpr int FS = QX + NX;
   static constexpr int W = FS + NX;
@@ -177,6 +178,19 @@ ASLR_HD bool boxqp_solve(const double* H, const double* q, const double* lb, con
   return true;
 }
 
+// Strided loop of a thread group over n work items with a compile-time trip count (fully unrollable).
+#define ASLR_GFOR(e, n)                                                            \
+  _Pragma("unroll") for (int _m = 0, e = g.lane; _m < ((n) + G - 1) / G; ++_m, e += G) \
+    if (e < (n))
+
+#if defined(__CUDA_ARCH__)
+#define ASLR_PREFETCH_L1(p) asm volatile("prefetch.global.L1 [%0];" ::"l"(p))
+#define ASLR_PREFETCH_L2(p) asm volatile("prefetch.global.L2 [%0];" ::"l"(p))
+#else
+#define ASLR_PREFETCH_L1(p) ((void)0)
+#define ASLR_PREFETCH_L2(p) ((void)0)
+#endif
+
 // One backward sweep with the current regularisation.  Returns false on "backward_error".
 template <class Grp, int NX, int NU>
 ASLR_HD bool backward_sweep(const Grp& g, double* sm, const SolverArgs& a, int b, const double* u_lb,
@@ -184,6 +198,7 @@ ASLR_HD bool backward_sweep(const Grp& g, double* sm, const SolverArgs& a, int b
   typedef BwdSmem<NX, NU> SM;
   typedef Rec<NX, NU> RC;
   constexpr int G = Grp::G;
+  constexpr int LINES = (RC::SIZE * 8 + 127) / 128;  // 128-byte lines of one knot record
   const int T = a.T;
   const AslrOcpState& st = a.buf.state[b];
   const bool feasible = st.is_feasible != 0;
@@ -198,25 +213,26 @@ ASLR_HD bool backward_sweep(const Grp& g, double* sm, const SolverArgs& a, int b
   // ---- terminal node: Vxx = Lxx + xreg I, Vx = Lx (+ Vxx fs)
   {
     const double* rec = deriv + (size_t)T * RC::SIZE;
-    for (int e = g.lane; e < NX * NX; e += G) Vxx[e] = rec[RC::LXX + e] + ((e / NX == e % NX) ? xreg : 0.0);
-    for (int e = g.lane; e < NX; e += G) Vx[e] = rec[RC::LX + e], sm[SM::FS + e] = fs[T * NX + e];
+    ASLR_GFOR(e, LINES) ASLR_PREFETCH_L1(deriv + (size_t)(T - 1) * RC::SIZE + e * 16);
+    ASLR_GFOR(e, NX * NX) Vxx[e] = rec[RC::LXX + e] + ((e / NX == e % NX) ? xreg : 0.0);
+    ASLR_GFOR(e, NX) Vx[e] = rec[RC::LX + e], sm[SM::FS + e] = fs[T * NX + e];
     if (g.lane == 0) flag[0] = 0.0;
     g.sync();
-    for (int e = g.lane; e < NX; e += G) {
+    ASLR_GFOR(e, NX) {
       double w = 0.0;
       if (!feasible) {
+#pragma unroll
         for (int k = 0; k < NX; ++k) w += Vxx[e * NX + k] * sm[SM::FS + k];
       }
       sm[SM::W + e] = w;
     }
     g.sync();
-    for (int e = g.lane; e < NX; e += G) {
+    ASLR_GFOR(e, NX) {
       Vx[e] += sm[SM::W + e];
       a.buf.Vx[((size_t)b * (T + 1) + T) * NX + e] = Vx[e];
       a.buf.Vxxfs[((size_t)b * (T + 1) + T) * NX + e] = sm[SM::W + e];
     }
-    if (a.buf.Vxx)
-      for (int e = g.lane; e < NX * NX; e += G) a.buf.Vxx[((size_t)b * (T + 1) + T) * NX * NX + e] = Vxx[e];
+    if (a.buf.Vxx) ASLR_GFOR(e, NX * NX) a.buf.Vxx[((size_t)b * (T + 1) + T) * NX * NX + e] = Vxx[e];
     g.sync();
     if (g.lane == 0 && !feasible) {
       for (int k = 0; k < NX; ++k) dgf -= Vx[k] * sm[SM::FS + k], dqf += sm[SM::FS + k] * sm[SM::W + k];
@@ -225,79 +241,114 @@ ASLR_HD bool backward_sweep(const Grp& g, double* sm, const SolverArgs& a, int b
 
   for (int t = T - 1; t >= 0; --t) {
     const double* rec = deriv + (size_t)t * RC::SIZE;
-    // ---- load the knot record
-    for (int e = g.lane; e < NX * NX; e += G) sm[SM::FX + e] = rec[RC::FX + e], sm[SM::QXX + e] = rec[RC::LXX + e];
-    for (int e = g.lane; e < NX * NU; e += G) sm[SM::FU + e] = rec[RC::FU + e], sm[SM::QXU + e] = rec[RC::LXU + e];
-    for (int e = g.lane; e < NU * NU; e += G) sm[SM::QUU + e] = rec[RC::LUU + e];
-    for (int e = g.lane; e < NX; e += G) sm[SM::QX + e] = rec[RC::LX + e], sm[SM::FS + e] = fs[t * NX + e];
-    for (int e = g.lane; e < NU; e += G) sm[SM::QU + e] = rec[RC::LU + e];
+    // ---- load the knot record (prefetched into L1 one knot ahead, into L2 two knots ahead)
+    if (t >= 1) ASLR_GFOR(e, LINES) ASLR_PREFETCH_L1(rec - RC::SIZE + e * 16);
+    if (t >= 2) ASLR_GFOR(e, LINES) ASLR_PREFETCH_L2(rec - 2 * RC::SIZE + e * 16);
+    ASLR_GFOR(e, NX * NX) sm[SM::FX + e] = rec[RC::FX + e], sm[SM::QXX + e] = rec[RC::LXX + e];
+    ASLR_GFOR(e, NX * NU) sm[SM::FU + e] = rec[RC::FU + e], sm[SM::QXU + e] = rec[RC::LXU + e];
+    ASLR_GFOR(e, NU * NU) sm[SM::QUU + e] = rec[RC::LUU + e];
+    ASLR_GFOR(e, NX) sm[SM::QX + e] = rec[RC::LX + e], sm[SM::FS + e] = feasible ? 0.0 : fs[t * NX + e];
+    ASLR_GFOR(e, NU) sm[SM::QU + e] = rec[RC::LU + e];
     g.sync();
     // ---- A = Fx^T Vxx', FuV = Fu^T Vxx', Qx += Fx^T Vx', Qu += Fu^T Vx'
-    for (int e = g.lane; e < NX * NX; e += G) {
+    ASLR_GFOR(e, NX * NX) {
       const int i = e / NX, j = e % NX;
       double s = 0.0;
+#pragma unroll
       for (int k = 0; k < NX; ++k) s += sm[SM::FX + k * NX + i] * Vxx[k * NX + j];
       sm[SM::A + e] = s;
     }
-    for (int e = g.lane; e < NU * NX; e += G) {
+    ASLR_GFOR(e, NU * NX) {
       const int i = e / NX, j = e % NX;
       double s = 0.0;
+#pragma unroll
       for (int k = 0; k < NX; ++k) s += sm[SM::FU + k * NU + i] * Vxx[k * NX + j];
       sm[SM::FUV + e] = s;
     }
-    for (int e = g.lane; e < NX + NU; e += G) {
+    ASLR_GFOR(e, NX + NU) {
       double s = 0.0;
       if (e < NX) {
+#pragma unroll
         for (int k = 0; k < NX; ++k) s += sm[SM::FX + k * NX + e] * Vx[k];
         sm[SM::QX + e] += s;
       } else {
+#pragma unroll
         for (int k = 0; k < NX; ++k) s += sm[SM::FU + k * NU + (e - NX)] * Vx[k];
         sm[SM::QU + (e - NX)] += s;
       }
     }
     g.sync();
     // ---- Qxx += A Fx, Qxu += A Fu, Quu += FuV Fu + ureg I
-    for (int e = g.lane; e < NX * NX; e += G) {
+    ASLR_GFOR(e, NX * NX) {
       const int i = e / NX, j = e % NX;
       double s = 0.0;
+#pragma unroll
       for (int k = 0; k < NX; ++k) s += sm[SM::A + i * NX + k] * sm[SM::FX + k * NX + j];
       sm[SM::QXX + e] += s;
     }
-    for (int e = g.lane; e < NX * NU; e += G) {
+    ASLR_GFOR(e, NX * NU) {
       const int i = e / NU, j = e % NU;
       double s = 0.0;
+#pragma unroll
       for (int k = 0; k < NX; ++k) s += sm[SM::A + i * NX + k] * sm[SM::FU + k * NU + j];
       sm[SM::QXU + e] += s;
     }
-    for (int e = g.lane; e < NU * NU; e += G) {
+    ASLR_GFOR(e, NU * NU) {
       const int i = e / NU, j = e % NU;
       double s = 0.0;
+#pragma unroll
       for (int k = 0; k < NX; ++k) s += sm[SM::FUV + i * NX + k] * sm[SM::FU + k * NU + j];
       sm[SM::QUU + e] += s + ((i == j) ? xreg : 0.0);
     }
     g.sync();
     // ---- computeGains
     if (!use_box) {
-      if (g.lane == 0) {
-        double* Lc = sm + SM::LC;
-        for (int e = 0; e < NU * NU; ++e) Lc[e] = sm[SM::QUU + e];
-        if (!cholesky<NU>(Lc)) flag[0] = 1.0;
-      }
-      g.sync();
-      if (flag[0] != 0.0) return false;
-      // K = Quu^-1 Qxu^T (one column per thread), k = Quu^-1 Qu
-      for (int e = g.lane; e < NX + 1; e += G) {
-        double col[NU];
-        for (int r = 0; r < NU; ++r) col[r] = (e < NX) ? sm[SM::QXU + e * NU + r] : sm[SM::QU + r];
-        chol_solve<NU>(sm + SM::LC, col);
-        for (int r = 0; r < NU; ++r) {
-          if (e < NX)
-            sm[SM::KG + r * NX + e] = col[r];
-          else
-            sm[SM::KF + r] = col[r];
+      if (NU <= 4) {
+        // tiny Quu: every column-solver thread factorises it redundantly (saves a phase and a barrier)
+        bool ok = true;
+        ASLR_GFOR(e, NX + 1) {
+          double Lc[NU * NU], Li[NU], col[NU];
+#pragma unroll
+          for (int r = 0; r < NU * NU; ++r) Lc[r] = sm[SM::QUU + r];
+          ok = cholesky<NU>(Lc, Li);
+#pragma unroll
+          for (int r = 0; r < NU; ++r) col[r] = (e < NX) ? sm[SM::QXU + e * NU + r] : sm[SM::QU + r];
+          chol_solve<NU>(Lc, Li, col);
+#pragma unroll
+          for (int r = 0; r < NU; ++r) {
+            if (e < NX)
+              sm[SM::KG + r * NX + e] = col[r];
+            else
+              sm[SM::KF + r] = col[r];
+          }
         }
+        if (!ok) flag[0] = 1.0;
+        g.sync();
+        if (flag[0] != 0.0) return false;
+      } else {
+        if (g.lane == 0) {
+          double* Lc = sm + SM::LC;
+          for (int e = 0; e < NU * NU; ++e) Lc[e] = sm[SM::QUU + e];
+          if (!cholesky<NU>(Lc, sm + SM::LINV)) flag[0] = 1.0;
+        }
+        g.sync();
+        if (flag[0] != 0.0) return false;
+        // K = Quu^-1 Qxu^T (one column per thread), k = Quu^-1 Qu
+        ASLR_GFOR(e, NX + 1) {
+          double col[NU];
+#pragma unroll
+          for (int r = 0; r < NU; ++r) col[r] = (e < NX) ? sm[SM::QXU + e * NU + r] : sm[SM::QU + r];
+          chol_solve<NU>(sm + SM::LC, sm + SM::LINV, col);
+#pragma unroll
+          for (int r = 0; r < NU; ++r) {
+            if (e < NX)
+              sm[SM::KG + r * NX + e] = col[r];
+            else
+              sm[SM::KF + r] = col[r];
+          }
+        }
+        g.sync();
       }
-      g.sync();
     } else {
       if (g.lane == 0) {
         double lb[NU], ub[NU], xq[NU], kinit[NU];
@@ -313,72 +364,89 @@ ASLR_HD bool backward_sweep(const Grp& g, double* sm, const SolverArgs& a, int b
       }
       g.sync();
       if (flag[0] != 0.0) return false;
-      for (int e = g.lane; e < NU * NX; e += G) {
+      ASLR_GFOR(e, NU * NX) {
         const int r = e / NX, c = e % NX;
         double s = 0.0;
+#pragma unroll
         for (int k = 0; k < NU; ++k) s += sm[SM::LC + r * NU + k] * sm[SM::QXU + c * NU + k];
         sm[SM::KG + e] = s;
       }
       g.sync();
     }
     // ---- Quuk = Quu k
-    for (int e = g.lane; e < NU; e += G) {
+    ASLR_GFOR(e, NU) {
       double s = 0.0;
+#pragma unroll
       for (int k = 0; k < NU; ++k) s += sm[SM::QUU + e * NU + k] * sm[SM::KF + k];
       sm[SM::QUUK + e] = s;
     }
-    g.sync();
+    if (NU > 4) g.sync();
     // ---- Vx = Qx + K^T Quuk - 2 K^T Qu ; Vtmp = Qxx - Qxu K  (into A)
-    for (int e = g.lane; e < NX; e += G) {
+    ASLR_GFOR(e, NX) {
       double s1 = 0.0, s2 = 0.0;
-      for (int k = 0; k < NU; ++k) s1 += sm[SM::KG + k * NX + e] * sm[SM::QUUK + k], s2 += sm[SM::KG + k * NX + e] * sm[SM::QU + k];
+#pragma unroll
+      for (int k = 0; k < NU; ++k) {
+        double qk;
+        if (NU <= 4) {  // recompute Quuk[k] locally instead of waiting for the phase above
+          qk = 0.0;
+#pragma unroll
+          for (int j = 0; j < NU; ++j) qk += sm[SM::QUU + k * NU + j] * sm[SM::KF + j];
+        } else {
+          qk = sm[SM::QUUK + k];
+        }
+        s1 += sm[SM::KG + k * NX + e] * qk, s2 += sm[SM::KG + k * NX + e] * sm[SM::QU + k];
+      }
       Vx[e] = (sm[SM::QX + e] + s1) - 2.0 * s2;
     }
-    for (int e = g.lane; e < NX * NX; e += G) {
+    ASLR_GFOR(e, NX * NX) {
       const int i = e / NX, j = e % NX;
       double s = 0.0;
+#pragma unroll
       for (int k = 0; k < NU; ++k) s += sm[SM::QXU + i * NU + k] * sm[SM::KG + k * NX + j];
       sm[SM::A + e] = sm[SM::QXX + e] - s;
     }
     g.sync();
-    // ---- symmetrise + xreg
-    for (int e = g.lane; e < NX * NX; e += G) {
+    // ---- symmetrise + xreg, NaN / inf check of Vxx
+    ASLR_GFOR(e, NX * NX) {
       const int i = e / NX, j = e % NX;
-      Vxx[e] = 0.5 * (sm[SM::A + e] + sm[SM::A + j * NX + i]) + ((i == j) ? xreg : 0.0);
+      const double v = 0.5 * (sm[SM::A + e] + sm[SM::A + j * NX + i]) + ((i == j) ? xreg : 0.0);
+      Vxx[e] = v;
+      if (isnan(v) || bad_value(fabs(v))) flag[0] = 1.0;
     }
-    g.sync();
-    // ---- w = Vxx fs ; Vx += w (infeasible only) ; NaN / inf check
-    for (int e = g.lane; e < NX; e += G) {
-      double w = 0.0;
-      if (!feasible) {
+    if (!feasible) {
+      g.sync();
+      // ---- w = Vxx fs ; Vx += w (infeasible iterations only)
+      ASLR_GFOR(e, NX) {
+        double w = 0.0;
+#pragma unroll
         for (int k = 0; k < NX; ++k) w += Vxx[e * NX + k] * sm[SM::FS + k];
+        sm[SM::W + e] = w;
+        Vx[e] += w;
       }
-      sm[SM::W + e] = w;
-      Vx[e] += w;
-      double m = fabs(Vx[e]);
-      bool nan = isnan(Vx[e]);
-      for (int k = 0; k < NX; ++k) m = fmax(m, fabs(Vxx[e * NX + k])), nan = nan || isnan(Vxx[e * NX + k]);
-      if (nan || bad_value(m)) flag[0] = 1.0;
+    } else {
+      ASLR_GFOR(e, NX) sm[SM::W + e] = 0.0;
+    }
+    ASLR_GFOR(e, NX) {
+      if (isnan(Vx[e]) || bad_value(fabs(Vx[e]))) flag[0] = 1.0;
     }
     g.sync();
     if (flag[0] != 0.0) return false;
     // ---- store
     {
       const size_t bt = (size_t)b * T + t;
-      for (int e = g.lane; e < NU * NX; e += G) a.buf.Kgain[bt * NU * NX + e] = sm[SM::KG + e];
-      for (int e = g.lane; e < NU; e += G) {
+      ASLR_GFOR(e, NU * NX) a.buf.Kgain[bt * NU * NX + e] = sm[SM::KG + e];
+      ASLR_GFOR(e, NU) {
         a.buf.kff[bt * NU + e] = sm[SM::KF + e];
         a.buf.Qu[bt * NU + e] = sm[SM::QU + e];
         a.buf.Quuk[bt * NU + e] = sm[SM::QUUK + e];
       }
-      if (a.buf.Quu)
-        for (int e = g.lane; e < NU * NU; e += G) a.buf.Quu[bt * NU * NU + e] = sm[SM::QUU + e];
+      if (a.buf.Quu) ASLR_GFOR(e, NU * NU) a.buf.Quu[bt * NU * NU + e] = sm[SM::QUU + e];
       const size_t bt1 = (size_t)b * (T + 1) + t;
-      for (int e = g.lane; e < NX; e += G) a.buf.Vx[bt1 * NX + e] = Vx[e], a.buf.Vxxfs[bt1 * NX + e] = sm[SM::W + e];
-      if (a.buf.Vxx)
-        for (int e = g.lane; e < NX * NX; e += G) a.buf.Vxx[bt1 * NX * NX + e] = Vxx[e];
+      ASLR_GFOR(e, NX) a.buf.Vx[bt1 * NX + e] = Vx[e], a.buf.Vxxfs[bt1 * NX + e] = sm[SM::W + e];
+      if (a.buf.Vxx) ASLR_GFOR(e, NX * NX) a.buf.Vxx[bt1 * NX * NX + e] = Vxx[e];
     }
     if (g.lane == 0) {
+#pragma unroll
       for (int k = 0; k < NU; ++k) {
         stop += sm[SM::QU + k] * sm[SM::QU + k];
         d1 += sm[SM::QU + k] * sm[SM::KF + k];

@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(128) solver_calcdiff_kernel(const __grid_const
 }
 
 template <int N, int NU, bool VSA>
-__global__ void __launch_bounds__(64) rollout_kernel(const __grid_constant__ DevProblem<N> P, const SolverArgs a) {
+__global__ void __launch_bounds__(64, (N <= 2) ? 5 : 1) rollout_kernel(const __grid_constant__ DevProblem<N> P, const SolverArgs a) {
   const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= (long)a.B * ASLR_NUM_ALPHAS) return;
   rollout_body<N, NU, VSA>(P, a, (int)(g / ASLR_NUM_ALPHAS), (int)(g % ASLR_NUM_ALPHAS));

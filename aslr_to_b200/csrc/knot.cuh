@@ -127,7 +127,8 @@ ASLR_HD void knot_eval(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
   double L[N * N];
 #pragma unroll
   for (int i = 0; i < N * N; ++i) L[i] = M[i];
-  cholesky<N>(L);
+  double Linv[N];
+  cholesky<N>(L, Linv);
   double al[N], am[N], Minv[DIFF ? N * N : 1];
   if (DIFF) {
     // explicit inverse, as the reference does (free_fwddyn_asr.py:40)
@@ -136,7 +137,7 @@ ASLR_HD void knot_eval(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
       double e[N];
 #pragma unroll
       for (int k = 0; k < N; ++k) e[k] = (k == c) ? 1.0 : 0.0;
-      chol_solve<N>(L, e);
+      chol_solve<N>(L, Linv, e);
 #pragma unroll
       for (int k = 0; k < N; ++k) Minv[k * N + c] = e[k];
     }
@@ -150,7 +151,7 @@ ASLR_HD void knot_eval(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
   } else {
 #pragma unroll
     for (int i = 0; i < N; ++i) al[i] = -nle[i] - tauc[i];
-    chol_solve<N>(L, al);
+    chol_solve<N>(L, Linv, al);
   }
 #pragma unroll
   for (int i = 0; i < N; ++i) {

@@ -142,6 +142,21 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
   double cost_try = 0.0, dv = 0.0;
   bool ok = true;
   for (int t = 0; t < T; ++t) {
+#if defined(__CUDA_ARCH__)
+    if (t + 1 < T) {  // pull the next step's gains / candidate into L1 while this step's dynamics run
+#pragma unroll
+      for (int l = 0; l < (NU * NX * 8 + 127) / 128; ++l)
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(Kg + (size_t)(t + 1) * NU * NX + l * 16));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(xs + (size_t)(t + 1) * NX));
+      if (NX > 16) asm volatile("prefetch.global.L1 [%0];" ::"l"(xs + (size_t)(t + 1) * NX + 16));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(us + (size_t)(t + 1) * NU));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(kf + (size_t)(t + 1) * NU));
+      if (gaps || need_dv) {
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(fs + (size_t)(t + 1) * NX));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(wv + (size_t)(t + 1) * NX));
+      }
+    }
+#endif
     double dx[NX];
 #pragma unroll
     for (int i = 0; i < NX; ++i) {

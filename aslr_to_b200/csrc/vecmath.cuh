@@ -131,11 +131,13 @@ ASLR_HD SI world_inertia(double mass, V3 c, const M3& Ic, const M3& R, V3 p) {
   return Y;
 }
 
-// In-place Cholesky A = L L^T of a dense symmetric N x N matrix (row-major, lower triangle used).
-// Returns false on a non-positive pivot, exactly like Eigen::LLT reports NumericalIssue (a NaN pivot
-// is not "<= 0" and passes through, as in Eigen).
+// In-place Cholesky A = L L^T of a dense symmetric N x N matrix (row-major, lower triangle used);
+// invd receives the reciprocals of the diagonal of L so that the triangular solves multiply instead of
+// divide (an FP64 division is a ~200-cycle dependent sequence on the GPU).  Returns false on a
+// non-positive pivot, exactly like Eigen::LLT reports NumericalIssue (a NaN pivot is not "<= 0" and passes
+// through, as in Eigen).
 template <int N>
-ASLR_HD bool cholesky(double* A) {
+ASLR_HD bool cholesky(double* A, double* invd) {
   bool ok = true;
 #pragma unroll
   for (int j = 0; j < N; ++j) {
@@ -145,7 +147,8 @@ ASLR_HD bool cholesky(double* A) {
     if (d <= 0.0) ok = false;
     d = sqrt(d);
     A[j * N + j] = d;
-    double inv = 1.0 / d;
+    const double inv = 1.0 / d;
+    invd[j] = inv;
 #pragma unroll
     for (int i = j + 1; i < N; ++i) {
       double s = A[i * N + j];
@@ -156,22 +159,22 @@ ASLR_HD bool cholesky(double* A) {
   }
   return ok;
 }
-// solve L L^T x = b in place (L from cholesky<N>)
+// solve L L^T x = b in place (L, invd from cholesky<N>)
 template <int N>
-ASLR_HD void chol_solve(const double* L, double* b) {
+ASLR_HD void chol_solve(const double* L, const double* invd, double* b) {
 #pragma unroll
   for (int i = 0; i < N; ++i) {
     double s = b[i];
 #pragma unroll
     for (int k = 0; k < i; ++k) s -= L[i * N + k] * b[k];
-    b[i] = s / L[i * N + i];
+    b[i] = s * invd[i];
   }
 #pragma unroll
   for (int i = N - 1; i >= 0; --i) {
     double s = b[i];
 #pragma unroll
     for (int k = i + 1; k < N; ++k) s -= L[k * N + i] * b[k];
-    b[i] = s / L[i * N + i];
+    b[i] = s * invd[i];
   }
 }
 

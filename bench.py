@@ -219,6 +219,26 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    if args.kernels:  # per-kernel CUDA-event timings of the first iterations (full batch active)
+        import ctypes as C
+        lib, bs, st = prob.lib, prob.batch_struct(), prob._stream()
+        opts = BT.make_opts(A.SOLVER_FDDP, w["maxiter"], w["th_stop"], lib=lib)
+        solver.t["xs"].copy_(d_xs0), solver.t["us"].copy_(d_us0)
+        A.check(lib.aslr_solver_init(prob.handle, C.byref(bs), C.byref(opts), C.byref(solver.buf), st))
+        rows = []
+        for it in range(args.kernels):
+            row = []
+            for fn, extra in ((lib.aslr_solver_calc_diff, (it,)), (lib.aslr_backward_pass, ()),
+                              (lib.aslr_forward_pass, ()), (lib.aslr_accept_step, (it,))):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                A.check(fn(prob.handle, C.byref(bs), C.byref(opts), C.byref(solver.buf), *extra, st))
+                e1.record()
+                torch.cuda.synchronize()
+                row.append(round(e0.elapsed_time(e1) * 1e3, 1))
+            rows.append(row)
+        print(json.dumps({"kernel_us_per_iteration[calcdiff,backward,rollout,accept]": rows}))
+        return
     if args.profile:  # for ncu: one warm-up solve, one profiled solve, nothing else
         step_device()
         torch.cuda.synchronize()
@@ -309,6 +329,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-ocps", type=int, default=2, help="OCPs in the bounded CPU-oracle sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--kernels", type=int, default=0, help="time each kernel of the first N iterations")
     ap.add_argument("--profile", action="store_true", help="two solves only (for ncu launch lists)")
     args = ap.parse_args()
     if args.impl == "reference":
