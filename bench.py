@@ -244,6 +244,9 @@ def run_ours(args):
         torch.cuda.synchronize()
         step_device()
         torch.cuda.synchronize()
+        for _ in range(2):  # the stand-alone fused calc+calcDiff sweep the roofline is quoted on
+            prob.calc_diff(solver.t["xs"], solver.t["us"])
+        torch.cuda.synchronize()
         print(json.dumps({"profile": True, "kernel_launches_per_solve": int(solver.result.kernel_launches)}))
         return
     for _ in range(max(args.warmup, 3)):
