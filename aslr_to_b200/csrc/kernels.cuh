@@ -18,18 +18,62 @@ struct KnotArgs {
 };
 
 // ------------------------------------------------------------------------------------------ K1
+// Coalesced record stores.  A thread-per-knot kernel that writes its own contiguous record issues
+// 8-byte stores 1392 bytes apart across the warp (32 sectors per instruction); ncu showed that LSU
+// pressure (lg_throttle) was the limiter.  Instead each warp stages the records of its 32 knots in
+// shared memory, one part of <= 64 doubles at a time, element-major with an odd stride (conflict-free
+// both ways), and writes every record part back as contiguous 256-byte rows.
+template <int SIZE>
+struct RecParts {
+  static constexpr int NP = (SIZE + 63) / 64;
+  static constexpr int LEN = ((SIZE + NP - 1) / NP + 1) & ~1;
+  static constexpr int STRIDE = 33;
+  static constexpr int WARP_DOUBLES = LEN * STRIDE;
+};
+
+template <int SIZE, int LO, int LEN>
+__device__ __forceinline__ void flush_part(const double* st, double* deriv, long g0, unsigned mask, int lane) {
+  constexpr int HI = (LO + LEN < SIZE) ? LO + LEN : SIZE;
+  __syncwarp();
+#pragma unroll 4
+  for (int r = 0; r < 32; ++r) {
+    if (!((mask >> r) & 1u)) continue;
+    double* o = deriv + (size_t)(g0 + r) * SIZE + LO;
+#pragma unroll
+    for (int e = lane; e < HI - LO; e += 32) o[e] = st[e * RecParts<SIZE>::STRIDE + r];
+  }
+  __syncwarp();
+}
+
+template <int N, int NU, int P>
+__device__ __forceinline__ void staged_record(double* st, double* deriv, long g0, unsigned mask, int lane, bool mine,
+                                              double dt, const KnotDeriv<N, NU>& kd) {
+  typedef Rec<4 * N, NU> RC;
+  typedef RecParts<RC::SIZE> RP;
+  if constexpr (P < RP::NP) {
+    constexpr int LO = P * RP::LEN;
+    if (mine) record_put<N, NU, LO, LO + RP::LEN>(st + lane - (size_t)LO * RP::STRIDE, RP::STRIDE, dt, kd);
+    flush_part<RC::SIZE, LO, RP::LEN>(st, deriv, g0, mask, lane);
+    staged_record<N, NU, P + 1>(st, deriv, g0, mask, lane, mine, dt, kd);
+  }
+}
+
 // stand-alone calc / calc+calcDiff sweep: one thread per knot (ShootingProblem.calc / calcDiff)
 template <int N, int NU, bool VSA, bool DIFF>
 __global__ void __launch_bounds__(128) knot_kernel(const __grid_constant__ DevProblem<N> P, const KnotArgs a) {
   constexpr int NX = 4 * N;
   typedef Rec<NX, NU> RC;
+  constexpr bool STAGED = DIFF && (N <= 2);
+  extern __shared__ double stage[];
   const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
   const long total = (long)a.B * (a.T + 1);
-  if (g >= total) return;
-  const int b = (int)(g / (a.T + 1)), t = (int)(g % (a.T + 1));
+  const bool live = g < total;
+  if (!STAGED && !live) return;
+  const long gc = live ? g : total - 1;
+  const int b = (int)(gc / (a.T + 1)), t = (int)(gc % (a.T + 1));
   const bool term = (t == a.T);
   double x[NX], u[NU], xn[NX], cost;
-  const double* xp = a.xs + (size_t)g * NX;
+  const double* xp = a.xs + (size_t)gc * NX;
 #pragma unroll
   for (int i = 0; i < NX; ++i) x[i] = xp[i];
   if (term || a.us == nullptr) {
@@ -42,12 +86,24 @@ __global__ void __launch_bounds__(128) knot_kernel(const __grid_constant__ DevPr
   }
   const double* Kocp = a.K_ocp ? a.K_ocp + (size_t)b * N * N : nullptr;
   const double* mref = a.mref_ocp ? a.mref_ocp + (size_t)b * 12 : nullptr;
-  double* rec = (DIFF && a.out.deriv) ? a.out.deriv + (size_t)g * RC::SIZE : nullptr;
-  double* xout = a.out.xout ? a.out.xout + (size_t)g * 2 * N : nullptr;
-  double* dFx = (DIFF && a.out.dFx) ? a.out.dFx + (size_t)g * 2 * N * NX : nullptr;
-  double* dFu = (DIFF && a.out.dFu) ? a.out.dFu + (size_t)g * 2 * N * NU : nullptr;
-  knot_eval<N, NU, VSA, DIFF>(P, term ? P.term : P.run, term ? P.dtT : P.dt, x, u, Kocp, mref, xn, cost, rec, xout,
-                              dFx, dFu);
+  double* xout = a.out.xout ? a.out.xout + (size_t)gc * 2 * N : nullptr;
+  double* dFx = (DIFF && a.out.dFx) ? a.out.dFx + (size_t)gc * 2 * N * NX : nullptr;
+  double* dFu = (DIFF && a.out.dFu) ? a.out.dFu + (size_t)gc * 2 * N * NU : nullptr;
+  const double dt = term ? P.dtT : P.dt;
+  if constexpr (STAGED) {
+    KnotDeriv<N, NU> kd;
+    if (live) knot_core<N, NU, VSA, true>(P, term ? P.term : P.run, dt, x, u, Kocp, mref, xn, cost, kd, xout, dFx, dFu);
+    if (a.out.deriv) {
+      const int lane = threadIdx.x & 31;
+      const unsigned mask = __ballot_sync(0xffffffffu, live);
+      staged_record<N, NU, 0>(stage + (size_t)(threadIdx.x >> 5) * RecParts<RC::SIZE>::WARP_DOUBLES, a.out.deriv,
+                              g - lane, mask, lane, live, dt, kd);
+    }
+    if (!live) return;
+  } else {
+    double* rec = (DIFF && a.out.deriv) ? a.out.deriv + (size_t)g * RC::SIZE : nullptr;
+    knot_eval<N, NU, VSA, DIFF>(P, term ? P.term : P.run, dt, x, u, Kocp, mref, xn, cost, rec, xout, dFx, dFu);
+  }
   if (a.out.cost) a.out.cost[g] = cost;
   if (a.out.xnext && !term) {
     double* xo = a.out.xnext + ((size_t)b * a.T + t) * NX;
@@ -60,9 +116,25 @@ __global__ void __launch_bounds__(128) knot_kernel(const __grid_constant__ DevPr
 template <int N, int NU, bool VSA>
 __global__ void __launch_bounds__(128) solver_calcdiff_kernel(const __grid_constant__ DevProblem<N> P,
                                                               const SolverArgs a) {
+  typedef Rec<4 * N, NU> RC;
+  extern __shared__ double stage[];
   const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= (long)a.B * (a.T + 1)) return;
-  calcdiff_body<N, NU, VSA>(P, a, (int)(g / (a.T + 1)), (int)(g % (a.T + 1)));
+  const long total = (long)a.B * (a.T + 1);
+  if constexpr (N <= 2) {
+    const bool live = g < total;
+    const long gc = live ? g : total - 1;
+    KnotDeriv<N, NU> kd;
+    double dt = 0.0;
+    const bool wrote = calcdiff_body<N, NU, VSA, true>(P, a, (int)(gc / (a.T + 1)), (int)(gc % (a.T + 1)), live, &kd, &dt);
+    const int lane = threadIdx.x & 31;
+    const unsigned mask = __ballot_sync(0xffffffffu, wrote);
+    if (mask)
+      staged_record<N, NU, 0>(stage + (size_t)(threadIdx.x >> 5) * RecParts<RC::SIZE>::WARP_DOUBLES, a.buf.deriv,
+                              g - lane, mask, lane, wrote, dt, kd);
+  } else {
+    if (g >= total) return;
+    calcdiff_body<N, NU, VSA, false>(P, a, (int)(g / (a.T + 1)), (int)(g % (a.T + 1)), true, nullptr, nullptr);
+  }
 }
 
 template <int N, int NU, bool VSA>
@@ -114,14 +186,22 @@ struct Launch {
   static constexpr int NX = 4 * N;
   static constexpr int NU = VSA ? 2 * N : N;
 
+  // shared-memory staging of the coalesced record stores (2-DOF kernels only)
+  static size_t stage_bytes(int threads) {
+    return (N <= 2) ? sizeof(double) * RecParts<Rec<NX, NU>::SIZE>::WARP_DOUBLES * (threads / 32) : 0;
+  }
   static int knots(const void* Pv, const KnotArgs& a, int diff, cudaStream_t s) {
     const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
     const long total = (long)a.B * (a.T + 1);
     if (total <= 0) return 0;
     const int threads = 128;
     const unsigned blocks = (unsigned)((total + threads - 1) / threads);
-    if (diff)
-      knot_kernel<N, NU, VSA, true><<<blocks, threads, 0, s>>>(P, a);
+    if (diff) {
+      if (N <= 2)
+        cudaFuncSetAttribute(knot_kernel<N, NU, VSA, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)stage_bytes(threads));
+      knot_kernel<N, NU, VSA, true><<<blocks, threads, stage_bytes(threads), s>>>(P, a);
+    }
     else
       knot_kernel<N, NU, VSA, false><<<blocks, threads, 0, s>>>(P, a);
     return launch_status();
@@ -130,7 +210,11 @@ struct Launch {
     const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
     const long total = (long)a.B * (a.T + 1);
     const int threads = 128;
-    solver_calcdiff_kernel<N, NU, VSA><<<(unsigned)((total + threads - 1) / threads), threads, 0, s>>>(P, a);
+    if (N <= 2)
+      cudaFuncSetAttribute(solver_calcdiff_kernel<N, NU, VSA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)stage_bytes(threads));
+    solver_calcdiff_kernel<N, NU, VSA>
+        <<<(unsigned)((total + threads - 1) / threads), threads, stage_bytes(threads), s>>>(P, a);
     return launch_status();
   }
   static int rollout(const void* Pv, const SolverArgs& a, cudaStream_t s) {

@@ -36,10 +36,19 @@ struct CostAcc {
 // Y_i-derivative applied to a motion m:  (S x* (Y m)) - Y (S x m), with Ym = Y m precomputed
 ASLR_HD SV dY_mul(const SI& Y, SV S, SV m, SV Ym) { return cross_mf(S, Ym) - mul(Y, cross_mm(S, m)); }
 
+// What calcDiff leaves behind for the record: the differential model's Jacobians and the cost sums.
+template <int N, int NU>
+struct KnotDeriv {
+  double AX[2 * N * 3 * N];  // d[a_l; a_m]/d[q_l q_m v_l]
+  double AU[2 * N * NU];     // d[a_l; a_m]/du
+  CostAcc<N> acc;
+};
+
+// calc (+ calcDiff up to the differential-model Jacobians and cost derivatives, left in `kd`)
 template <int N, int NU, bool VSA, bool DIFF>
-ASLR_HD void knot_eval(const DevProblem<N>& P, const DevCostSum<N>& C, const double dt, const double* x,
+ASLR_HD void knot_core(const DevProblem<N>& P, const DevCostSum<N>& C, const double dt, const double* x,
                        const double* u, const double* Kocp, const double* mref, double* xnext, double& cost_out,
-                       double* rec, double* xout, double* dFx, double* dFu) {
+                       KnotDeriv<N, NU>& kd, double* xout, double* dFx, double* dFu) {
   constexpr int NX = 4 * N;
   const double* ql = x;
   const double* qm = x + N;
@@ -184,7 +193,7 @@ ASLR_HD void knot_eval(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
 
   // ---------------------------------------------------------------- costs (crocoddyl.CostModelSum)
   double cost = 0.0;
-  CostAcc<N> acc;
+  CostAcc<N>& acc = kd.acc;
   if (DIFF) {
 #pragma unroll
     for (int i = 0; i < NX; ++i) acc.Lx[i] = 0, acc.Lxxd[i] = 0;
@@ -392,7 +401,8 @@ ASLR_HD void knot_eval(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
 #pragma unroll
     for (int i = 0; i < N; ++i) Kmat[i * N + i] = u[N + i];
   }
-  double AX[2 * N * 3 * N], AU[2 * N * NU];
+  double* AX = kd.AX;
+  double* AU = kd.AU;
 #pragma unroll
   for (int i = 0; i < N; ++i) {
 #pragma unroll
@@ -441,25 +451,36 @@ ASLR_HD void knot_eval(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
 #pragma unroll
     for (int i = 0; i < 2 * N * NU; ++i) dFu[i] = AU[i];
   }
-  if (!rec) return;
+}
 
-  // ---------------------------------------------------------------- action-model record
-  // Fx = I + dt [[dt a_x + [0 I]], [a_x]],  Fu = [dt^2 a_u; dt a_u]   (integrated_action.py:31-37);
-  // L* copied unscaled (integrated_action.py:38-42)
+// Elements [LO, HI) of the action-model record, element e stored at rec[e * stride]:
+//   Fx = I + dt [[dt a_x + [0 I]], [a_x]],  Fu = [dt^2 a_u; dt a_u]   (integrated_action.py:31-37);
+//   L* copied unscaled (integrated_action.py:38-42).
+// Every index below is a compile-time constant after unrolling, so the range test costs nothing.
+#define ASLR_PUT(idx, val)                                      \
+  do {                                                          \
+    if ((idx) >= LO && (idx) < HI) rec[(size_t)(idx) * stride] = (val); \
+  } while (0)
+template <int N, int NU, int LO, int HI>
+ASLR_HD void record_put(double* rec, const int stride, const double dt, const KnotDeriv<N, NU>& kd) {
+  constexpr int NX = 4 * N;
   typedef Rec<NX, NU> RC;
+  const double* AX = kd.AX;
+  const double* AU = kd.AU;
+  const CostAcc<N>& acc = kd.acc;
   const double dt2 = dt * dt;
 #pragma unroll
   for (int r = 0; r < 2 * N; ++r) {
 #pragma unroll
     for (int c = 0; c < NX; ++c) {
       const double ax = (c < 3 * N) ? AX[r * 3 * N + (c < 3 * N ? c : 0)] : 0.0;
-      rec[RC::FX + r * NX + c] = ((r == c) ? 1.0 : 0.0) + dt2 * ax + ((c == r + 2 * N) ? dt : 0.0);
-      rec[RC::FX + (2 * N + r) * NX + c] = ((2 * N + r == c) ? 1.0 : 0.0) + dt * ax;
+      ASLR_PUT(RC::FX + r * NX + c, ((r == c) ? 1.0 : 0.0) + dt2 * ax + ((c == r + 2 * N) ? dt : 0.0));
+      ASLR_PUT(RC::FX + (2 * N + r) * NX + c, ((2 * N + r == c) ? 1.0 : 0.0) + dt * ax);
     }
 #pragma unroll
     for (int c = 0; c < NU; ++c) {
-      rec[RC::FU + r * NU + c] = dt2 * AU[r * NU + c];
-      rec[RC::FU + (2 * N + r) * NU + c] = dt * AU[r * NU + c];
+      ASLR_PUT(RC::FU + r * NU + c, dt2 * AU[r * NU + c]);
+      ASLR_PUT(RC::FU + (2 * N + r) * NU + c, dt * AU[r * NU + c]);
     }
   }
 #pragma unroll
@@ -468,18 +489,29 @@ ASLR_HD void knot_eval(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
     for (int c = 0; c < NX; ++c) {
       double val = (r == c) ? acc.Lxxd[r] : 0.0;
       if (r < N && c < N) val += acc.Lqq[(r < N ? r : 0) * N + (c < N ? c : 0)];
-      rec[RC::LXX + r * NX + c] = val;
+      ASLR_PUT(RC::LXX + r * NX + c, val);
     }
 #pragma unroll
-    for (int c = 0; c < NU; ++c) rec[RC::LXU + r * NU + c] = 0.0;  // no cost of the menu couples x and u
-    rec[RC::LX + r] = acc.Lx[r];
+    for (int c = 0; c < NU; ++c) ASLR_PUT(RC::LXU + r * NU + c, 0.0);  // no cost of the menu couples x and u
+    ASLR_PUT(RC::LX + r, acc.Lx[r]);
   }
 #pragma unroll
   for (int r = 0; r < NU; ++r) {
 #pragma unroll
-    for (int c = 0; c < NU; ++c) rec[RC::LUU + r * NU + c] = (r == c) ? acc.Luud[r] : 0.0;
-    rec[RC::LU + r] = acc.Lu[r];
+    for (int c = 0; c < NU; ++c) ASLR_PUT(RC::LUU + r * NU + c, (r == c) ? acc.Luud[r] : 0.0);
+    ASLR_PUT(RC::LU + r, acc.Lu[r]);
   }
+}
+#undef ASLR_PUT
+
+// knot_core + the whole record written straight to `rec` (contiguous)
+template <int N, int NU, bool VSA, bool DIFF>
+ASLR_HD void knot_eval(const DevProblem<N>& P, const DevCostSum<N>& C, const double dt, const double* x,
+                       const double* u, const double* Kocp, const double* mref, double* xnext, double& cost_out,
+                       double* rec, double* xout, double* dFx, double* dFu) {
+  KnotDeriv<N, NU> kd;
+  knot_core<N, NU, VSA, DIFF>(P, C, dt, x, u, Kocp, mref, xnext, cost_out, kd, xout, dFx, dFu);
+  if (DIFF && rec) record_put<N, NU, 0, Rec<4 * N, NU>::SIZE>(rec, 1, dt, kd);
 }
 
 }  // namespace aslr

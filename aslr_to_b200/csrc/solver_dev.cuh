@@ -38,15 +38,20 @@ ASLR_HD void init_body(const SolverArgs& a, int b) {
 // K1 in solver mode: adopt the accepted trial (setCandidate), calc + calcDiff, gaps
 // (SolverDDP::calcDiff + computeDynamicFeasibility, Appendix A.2).  One thread per knot.
 // ---------------------------------------------------------------------------------------------
-template <int N, int NU, bool VSA>
-ASLR_HD void calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, int t) {
+// STAGED = false: the record goes straight to a.buf.deriv.  STAGED = true (2-DOF CUDA kernels): the
+// Jacobians are left in *kd / *dt_out for the caller's coalesced shared-memory flush; the return value
+// says whether this knot has a record to write.  `live` = false marks a padding thread of the last CTA.
+template <int N, int NU, bool VSA, bool STAGED>
+ASLR_HD bool calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, int t, bool live, KnotDeriv<N, NU>* kd,
+                           double* dt_out) {
   constexpr int NX = 4 * N;
   typedef Rec<NX, NU> RC;
+  if (!live) return false;
   const AslrOcpState& s = a.buf.state[b];
   const int T = a.T;
   const int slot = s.src_slot;
   const bool running = (s.status == ASLR_OCP_RUNNING) && s.recalc;
-  if (slot < 0 && !running) return;
+  if (slot < 0 && !running) return false;
   double x[NX], u[NU];
   double* xs_b = a.buf.xs + ((size_t)b * (T + 1) + t) * NX;
   double* us_b = a.buf.us + ((size_t)b * T + (t < T ? t : 0)) * NU;
@@ -67,7 +72,7 @@ ASLR_HD void calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, i
       for (int i = 0; i < NU; ++i) u[i] = us_b[i];
     }
   }
-  if (!running) return;
+  if (!running) return false;
   if (t == T) {
 #pragma unroll
     for (int i = 0; i < NU; ++i) u[i] = P.u_none[i];  // terminal node: u is None
@@ -75,9 +80,16 @@ ASLR_HD void calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, i
   double xn[NX], cost;
   const double* Kocp = a.K_ocp ? a.K_ocp + (size_t)b * N * N : nullptr;
   const double* mref = a.mref_ocp ? a.mref_ocp + (size_t)b * 12 : nullptr;
-  double* rec = a.buf.deriv + ((size_t)b * (T + 1) + t) * RC::SIZE;
-  knot_eval<N, NU, VSA, true>(P, t == T ? P.term : P.run, t == T ? P.dtT : P.dt, x, u, Kocp, mref, xn, cost, rec,
-                              nullptr, nullptr, nullptr);
+  const double dt = (t == T) ? P.dtT : P.dt;
+  if (STAGED) {
+    *dt_out = dt;
+    knot_core<N, NU, VSA, true>(P, t == T ? P.term : P.run, dt, x, u, Kocp, mref, xn, cost, *kd, nullptr, nullptr,
+                                nullptr);
+  } else {
+    double* rec = a.buf.deriv + ((size_t)b * (T + 1) + t) * RC::SIZE;
+    knot_eval<N, NU, VSA, true>(P, t == T ? P.term : P.run, dt, x, u, Kocp, mref, xn, cost, rec, nullptr, nullptr,
+                                nullptr);
+  }
   a.buf.knot_cost[(size_t)b * (T + 1) + t] = cost;
   if (t < T) {
     double* xo = a.buf.xnext + ((size_t)b * T + t) * NX;
@@ -106,6 +118,12 @@ ASLR_HD void calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, i
       for (int i = 0; i < NX; ++i) fs[i] = 0.0;
     }
   }
+  return true;
+}
+
+template <int N, int NU, bool VSA>
+ASLR_HD void calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, int t) {
+  calcdiff_body<N, NU, VSA, false>(P, a, b, t, true, nullptr, nullptr);
 }
 
 // ---------------------------------------------------------------------------------------------
