@@ -127,7 +127,8 @@ _PROTOS = {
 
 EXPORTED_SYMBOLS = tuple(sorted(_PROTOS))
 LIB_NAME = "libaslr_b200.so"
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)
+LIB_PATH = os.environ.get("ASLR_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)
+# (ASLR_B200_LIB: tuning builds of the same library, tools/build_variant.sh)
 
 _lib = None
 

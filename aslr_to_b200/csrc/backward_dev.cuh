@@ -21,6 +21,14 @@ struct GrpWarp {
   int lane;
   __device__ __forceinline__ void sync() const { __syncwarp(); }
 };
+// GS lanes of a warp (GS = 8, 16 or 32): several OCPs share a warp, each group synchronising on its own lane mask
+template <int GS>
+struct GrpSub {
+  static constexpr int G = GS;
+  int lane;
+  unsigned mask;
+  __device__ __forceinline__ void sync() const { __syncwarp(mask); }
+};
 template <int THREADS>
 struct GrpCta {
   static constexpr int G = THREADS;

@@ -6,6 +6,14 @@
 
 #include "backward_dev.cuh"
 
+#ifndef ASLR_ROLL_THREADS
+#define ASLR_ROLL_THREADS 64  // 2-DOF rollout: CTA size and minimum resident CTAs per SM (one wave for 40960 trials)
+#define ASLR_ROLL_MINB 5
+#endif
+#ifndef ASLR_BWD_GS
+#define ASLR_BWD_GS 16  // lanes per OCP in the nx = 8 backward pass
+#endif
+
 namespace aslr {
 
 struct KnotArgs {
@@ -138,7 +146,7 @@ __global__ void __launch_bounds__(128) solver_calcdiff_kernel(const __grid_const
 }
 
 template <int N, int NU, bool VSA>
-__global__ void __launch_bounds__(64, (N <= 2) ? 5 : 1) rollout_kernel(const __grid_constant__ DevProblem<N> P, const SolverArgs a) {
+__global__ void __launch_bounds__((N <= 2) ? ASLR_ROLL_THREADS : 64, (N <= 2) ? ASLR_ROLL_MINB : 1) rollout_kernel(const __grid_constant__ DevProblem<N> P, const SolverArgs a) {
   const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= (long)a.B * ASLR_NUM_ALPHAS) return;
   rollout_body<N, NU, VSA>(P, a, (int)(g / ASLR_NUM_ALPHAS), (int)(g % ASLR_NUM_ALPHAS));
@@ -150,16 +158,18 @@ struct BoxLimits {
   double lb[NU], ub[NU];
 };
 
-// warp per OCP (small nx): WARPS OCPs per CTA, each with its own shared-memory slice
-template <int NX, int NU, int WARPS>
-__global__ void __launch_bounds__(32 * WARPS) backward_warp_kernel(const SolverArgs a, const BoxLimits<NU> lim) {
+// sub-warp group per OCP (small nx): GS lanes per OCP, GROUPS OCPs per CTA, each with its own shared-memory slice
+template <int NX, int NU, int GS, int GROUPS>
+__global__ void __launch_bounds__(GS * GROUPS) backward_warp_kernel(const SolverArgs a, const BoxLimits<NU> lim) {
   extern __shared__ double smem[];
-  const int w = threadIdx.x >> 5;
-  const int b = blockIdx.x * WARPS + w;
+  const int w = threadIdx.x / GS;
+  const int b = blockIdx.x * GROUPS + w;
   if (b >= a.B) return;
-  GrpWarp g{(int)(threadIdx.x & 31)};
-  backward_body<GrpWarp, NX, NU>(g, smem + (size_t)w * BwdSmem<NX, NU>::SIZE, a, b, lim.lb, lim.ub, lim.has != 0,
-                                 a.buf.counters);
+  const int lane = threadIdx.x % GS;
+  const unsigned mask = (GS == 32) ? 0xffffffffu : (((1u << GS) - 1u) << ((threadIdx.x & 31) - lane));
+  GrpSub<GS> g{lane, mask};
+  backward_body<GrpSub<GS>, NX, NU>(g, smem + (size_t)w * BwdSmem<NX, NU>::SIZE, a, b, lim.lb, lim.ub, lim.has != 0,
+                                    a.buf.counters);
 }
 
 // CTA per OCP (nx = 28)
@@ -220,7 +230,7 @@ struct Launch {
   static int rollout(const void* Pv, const SolverArgs& a, cudaStream_t s) {
     const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
     const long total = (long)a.B * ASLR_NUM_ALPHAS;
-    const int threads = 64;
+    const int threads = (N <= 2) ? ASLR_ROLL_THREADS : 64;
     rollout_kernel<N, NU, VSA><<<(unsigned)((total + threads - 1) / threads), threads, 0, s>>>(P, a);
     return launch_status();
   }
@@ -231,10 +241,10 @@ struct Launch {
     for (int i = 0; i < NU; ++i) lim.lb[i] = P.u_lb[i], lim.ub[i] = P.u_ub[i];
     constexpr size_t per = sizeof(double) * BwdSmem<NX, NU>::SIZE;
     if constexpr (NX <= 12) {
-      constexpr int WARPS = 4;
-      auto k = backward_warp_kernel<NX, NU, WARPS>;
-      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(per * WARPS));
-      k<<<(a.B + WARPS - 1) / WARPS, 32 * WARPS, per * WARPS, s>>>(a, lim);
+      constexpr int GS = ASLR_BWD_GS, GROUPS = 128 / GS;
+      auto k = backward_warp_kernel<NX, NU, GS, GROUPS>;
+      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(per * GROUPS));
+      k<<<(a.B + GROUPS - 1) / GROUPS, GS * GROUPS, per * GROUPS, s>>>(a, lim);
     } else {
       constexpr int THREADS = 128;
       auto k = backward_cta_kernel<NX, NU, THREADS>;
