@@ -111,6 +111,8 @@ _PROTOS = {
     "aslr_calc": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.c_void_p, C.c_void_p, C.POINTER(KnotOut), C.c_void_p]),
     "aslr_calc_diff": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.c_void_p, C.c_void_p, C.POINTER(KnotOut),
                                  C.c_void_p]),
+    "aslr_quasi_static": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.c_void_p, C.c_void_p, C.c_int32, C.c_double,
+                                    C.c_void_p]),
     "aslr_solver_init": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(SolverOpts), C.POINTER(SolverBuffers),
                                    C.c_void_p]),
     "aslr_solver_calc_diff": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(SolverOpts),

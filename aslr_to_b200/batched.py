@@ -135,6 +135,16 @@ class BatchedShootingProblem(object):
         """ShootingProblem.calc + calcDiff for every OCP (one fused kernel)."""
         return self._knots(self.lib.aslr_calc_diff, xs, us, want)
 
+    def quasi_static(self, xs, maxiter=100, tol=1e-9):
+        """ShootingProblem.quasiStatic for every OCP: xs (B, T, nx) -> us (B, T, nu), device tensor."""
+        torch = _torch()
+        xs = self._dev(xs, (self.B, self.T, self.nx))
+        us = torch.zeros((self.B, self.T, self.nu), dtype=torch.float64, device=self.device)
+        b = self.batch_struct()
+        A.check(self.lib.aslr_quasi_static(self.handle, C.byref(b), xs.data_ptr(), us.data_ptr(), int(maxiter),
+                                           float(tol), self._stream()))
+        return us
+
     def split_record(self, deriv):
         """(…, rec) tensor/array -> dict Fx, Fu, Lxx, Lxu, Luu, Lx, Lu."""
         nx, nu = self.nx, self.nu

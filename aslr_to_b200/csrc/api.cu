@@ -162,6 +162,17 @@ int aslr_calc_diff(const AslrProblem* p, const AslrBatch* batch, const double* x
   return knots(p, batch, xs, us, out, 1, stream);
 }
 
+int aslr_quasi_static(const AslrProblem* p, const AslrBatch* batch, const double* xs, double* us, int32_t maxiter,
+                      double tol, void* stream) {
+  if (!p || !batch || !xs || !us) return fail(ASLR_ERR_INVALID, "null argument%s");
+  if (batch->B < 0 || batch->T < 0 || maxiter < 0) return fail(ASLR_ERR_INVALID, "negative dimension%s");
+  KnotArgs a;
+  a.B = batch->B, a.T = batch->T, a.xs = xs, a.us = nullptr, a.K_ocp = batch->K_ocp, a.mref_ocp = batch->mref_ocp;
+  a.out = AslrKnotOut{};
+  if (p->fn.quasi_static(p->dev, a, us, maxiter, tol, (cudaStream_t)stream) != 0) return cuda_fail(cudaGetLastError());
+  return ASLR_OK;
+}
+
 static int make_args(const AslrProblem* p, const AslrBatch* batch, const AslrSolverOpts* opts,
                      const AslrSolverBuffers* buf, int iter, SolverArgs* a) {
   if (!p || !batch || !opts || !buf) return fail(ASLR_ERR_INVALID, "null argument%s");

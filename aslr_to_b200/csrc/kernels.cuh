@@ -152,6 +152,20 @@ __global__ void __launch_bounds__((N <= 2) ? ASLR_ROLL_THREADS : 64, (N <= 2) ? 
   rollout_body<N, NU, VSA>(P, a, (int)(g / ASLR_NUM_ALPHAS), (int)(g % ASLR_NUM_ALPHAS));
 }
 
+// quasiStatic of every running knot: one thread per (OCP, knot)
+template <int N, int NU, bool VSA>
+__global__ void __launch_bounds__(64) quasi_static_kernel(const __grid_constant__ DevProblem<N> P, const KnotArgs a,
+                                                          double* us, int maxiter, double tol) {
+  const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (long)a.B * a.T) return;
+  const int b = (int)(g / a.T);
+  double x[4 * N];
+#pragma unroll
+  for (int i = 0; i < 4 * N; ++i) x[i] = a.xs[(size_t)g * 4 * N + i];
+  quasi_static_body<N, NU, VSA>(P, x, a.K_ocp ? a.K_ocp + (size_t)b * N * N : nullptr,
+                                a.mref_ocp ? a.mref_ocp + (size_t)b * 12 : nullptr, maxiter, tol, us + (size_t)g * NU);
+}
+
 template <int NU>
 struct BoxLimits {
   int has;
@@ -187,6 +201,7 @@ struct Launchers {
   int (*calcdiff)(const void* P, const SolverArgs& a, cudaStream_t s);
   int (*backward)(const void* P, const SolverArgs& a, cudaStream_t s);
   int (*rollout)(const void* P, const SolverArgs& a, cudaStream_t s);
+  int (*quasi_static)(const void* P, const KnotArgs& a, double* us, int maxiter, double tol, cudaStream_t s);
 };
 
 inline int launch_status() { return cudaGetLastError() == cudaSuccess ? 0 : -2; }
@@ -253,7 +268,14 @@ struct Launch {
     }
     return launch_status();
   }
-  static Launchers table() { return Launchers{&knots, &calcdiff, &backward, &rollout}; }
+  static int quasi_static(const void* Pv, const KnotArgs& a, double* us, int maxiter, double tol, cudaStream_t s) {
+    const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
+    const long total = (long)a.B * a.T;
+    if (total <= 0) return 0;
+    quasi_static_kernel<N, NU, VSA><<<(unsigned)((total + 63) / 64), 64, 0, s>>>(P, a, us, maxiter, tol);
+    return launch_status();
+  }
+  static Launchers table() { return Launchers{&knots, &calcdiff, &backward, &rollout, &quasi_static}; }
 };
 
 // defined in inst_n*.cu

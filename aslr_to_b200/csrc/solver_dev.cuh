@@ -127,6 +127,97 @@ ASLR_HD void calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, i
 }
 
 // ---------------------------------------------------------------------------------------------
+// ActionModelAbstract::quasiStatic of one running knot (crocoddyl base class; the Python models of the
+// reference do not override it; call site examples/two_dof_sea.py:78):
+//   u = 0;  repeat { calc, calcDiff;  du = -pinv(Fu) diff(x, xnext);  u += du }  until |du| <= tol.
+// Fu = [dt^2 a_u; dt a_u], so pinv(Fu) r = (Fu^T Fu)^+ Fu^T r with the nu x nu Gram matrix
+// G = (dt^4 + dt^2) a_u^T a_u, whose pseudo-inverse comes from a cyclic Jacobi eigen-decomposition.
+// Rank decision: eigenvalues <= nu * eps * lambda_max count as zero (numpy.linalg.pinv cuts singular
+// values at 1e-15 s_max; the Gram form cannot resolve below ~sqrt(eps) s_max.  In every supported
+// model a deficient rank comes from exactly-zero columns of a_u, which stay exactly zero here).
+// One thread per knot.
+// ---------------------------------------------------------------------------------------------
+template <int NU>
+ASLR_HD void sym_pinv_apply(double* G, const double* g, double* out) {
+  // G (NU x NU, symmetric, destroyed) -> out = G^+ g
+  double V[NU * NU];
+#pragma unroll 1
+  for (int i = 0; i < NU * NU; ++i) V[i] = (i / NU == i % NU) ? 1.0 : 0.0;
+#pragma unroll 1
+  for (int sweep = 0; sweep < 30; ++sweep) {
+    double off = 0.0, diag = 0.0;
+    for (int i = 0; i < NU; ++i)
+      for (int j = 0; j < NU; ++j) (i == j ? diag : off) += G[i * NU + j] * G[i * NU + j];
+    if (off <= 1e-60 || off <= 1e-32 * diag) break;
+    for (int p = 0; p < NU - 1; ++p)
+      for (int q = p + 1; q < NU; ++q) {
+        const double apq = G[p * NU + q];
+        if (apq == 0.0) continue;
+        const double theta = (G[q * NU + q] - G[p * NU + p]) / (2.0 * apq);
+        const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+        const double c = 1.0 / sqrt(t * t + 1.0), sn = t * c;
+        for (int k = 0; k < NU; ++k) {  // columns p, q
+          const double gkp = G[k * NU + p], gkq = G[k * NU + q];
+          G[k * NU + p] = c * gkp - sn * gkq, G[k * NU + q] = sn * gkp + c * gkq;
+        }
+        for (int k = 0; k < NU; ++k) {  // rows p, q
+          const double gpk = G[p * NU + k], gqk = G[q * NU + k];
+          G[p * NU + k] = c * gpk - sn * gqk, G[q * NU + k] = sn * gpk + c * gqk;
+        }
+        for (int k = 0; k < NU; ++k) {
+          const double vkp = V[k * NU + p], vkq = V[k * NU + q];
+          V[k * NU + p] = c * vkp - sn * vkq, V[k * NU + q] = sn * vkp + c * vkq;
+        }
+      }
+  }
+  double lmax = 0.0;
+  for (int i = 0; i < NU; ++i) lmax = fmax(lmax, G[i * NU + i]);
+  const double thr = (double)NU * 2.220446049250313e-16 * lmax;
+  for (int i = 0; i < NU; ++i) out[i] = 0.0;
+  for (int e = 0; e < NU; ++e) {
+    const double lam = G[e * NU + e];
+    if (!(lam > thr)) continue;
+    double proj = 0.0;
+    for (int k = 0; k < NU; ++k) proj += V[k * NU + e] * g[k];
+    proj /= lam;
+    for (int k = 0; k < NU; ++k) out[k] += V[k * NU + e] * proj;
+  }
+}
+
+template <int N, int NU, bool VSA>
+ASLR_HD void quasi_static_body(const DevProblem<N>& P, const double* x, const double* Kocp, const double* mref,
+                               int maxiter, double tol, double* u_out) {
+  constexpr int NX = 4 * N;
+  double u[NU];
+  for (int i = 0; i < NU; ++i) u[i] = 0.0;
+  const double dt = P.dt, dt2 = dt * dt;
+#pragma unroll 1
+  for (int it = 0; it < maxiter; ++it) {
+    KnotDeriv<N, NU> kd;
+    double xn[NX], cost;
+    knot_core<N, NU, VSA, true>(P, P.run, dt, x, u, Kocp, mref, xn, cost, kd, nullptr, nullptr, nullptr);
+    // g = Fu^T (xnext - x) = a_u^T (dt^2 dx[:2n] + dt dx[2n:]),  G = (dt^4 + dt^2) a_u^T a_u
+    double r[2 * N], g[NU], G[NU * NU], du[NU];
+    for (int i = 0; i < 2 * N; ++i) r[i] = dt2 * (xn[i] - x[i]) + dt * (xn[2 * N + i] - x[2 * N + i]);
+    for (int a = 0; a < NU; ++a) {
+      double s = 0.0;
+      for (int i = 0; i < 2 * N; ++i) s += kd.AU[i * NU + a] * r[i];
+      g[a] = s;
+      for (int b = 0; b < NU; ++b) {
+        double q = 0.0;
+        for (int i = 0; i < 2 * N; ++i) q += kd.AU[i * NU + a] * kd.AU[i * NU + b];
+        G[a * NU + b] = (dt2 * dt2 + dt2) * q;
+      }
+    }
+    sym_pinv_apply<NU>(G, g, du);
+    double nrm = 0.0;
+    for (int i = 0; i < NU; ++i) u[i] -= du[i], nrm += du[i] * du[i];
+    if (sqrt(nrm) <= tol) break;
+  }
+  for (int i = 0; i < NU; ++i) u_out[i] = u[i];
+}
+
+// ---------------------------------------------------------------------------------------------
 // K3: one trial rollout = SolverDDP/FDDP/BoxDDP::forwardPass(alpha) (Appendix A.4) plus the
 // trial-dependent part of FDDP's expectedImprovement.  One thread per (OCP, alpha).
 // ---------------------------------------------------------------------------------------------

@@ -247,6 +247,13 @@ int aslr_calc(const AslrProblem* p, const AslrBatch* batch, const double* xs, co
 int aslr_calc_diff(const AslrProblem* p, const AslrBatch* batch, const double* xs, const double* us,
                    const AslrKnotOut* out, void* stream);
 
+/* ShootingProblem.quasiStatic(xs) (examples/two_dof_sea.py:78): crocoddyl's base-class
+ * ActionModelAbstract::quasiStatic of the running model at every state, u = 0 start,
+ * u <- u - pinv(Fu) diff(x, xnext) until |du| <= tol or maxiter (crocoddyl defaults 100, 1e-9).
+ * xs [B][T][nx] (one state per running knot), us [B][T][nu] (out). */
+int aslr_quasi_static(const AslrProblem* p, const AslrBatch* batch, const double* xs, double* us, int32_t maxiter,
+                      double tol, void* stream);
+
 /* One solver building block each; they operate on the per-OCP state in `buf` exactly like the
  * crocoddyl member functions of the same name. */
 int aslr_solver_init(const AslrProblem* p, const AslrBatch* batch, const AslrSolverOpts* opts,

@@ -92,3 +92,21 @@ extern "C" int hh_solve(const AslrProblemDesc* desc, const AslrBatch* batch, con
   if (n == 7) return vsa ? solve_t<7, true>(desc, batch, opts, buf, iters_out) : solve_t<7, false>(desc, batch, opts, buf, iters_out);
   return -1;
 }
+
+// quasiStatic of one running knot (same device body)
+template <int N, bool VSA>
+static int qs_t(const AslrProblemDesc* desc, const double* x, const double* Kocp, int maxiter, double tol, double* u) {
+  constexpr int NU = VSA ? 2 * N : N;
+  static DevProblem<N> P;
+  fill_dev_problem<N>(*desc, P);
+  quasi_static_body<N, NU, VSA>(P, x, Kocp, nullptr, maxiter, tol, u);
+  return 0;
+}
+extern "C" int hh_quasi_static(const AslrProblemDesc* desc, const double* x, const double* Kocp, int maxiter, double tol,
+                               double* u) {
+  const int n = desc->robot.n;
+  const bool vsa = desc->dyn.kind == ASLR_DYN_VSA;
+  if (n == 2) return vsa ? qs_t<2, true>(desc, x, Kocp, maxiter, tol, u) : qs_t<2, false>(desc, x, Kocp, maxiter, tol, u);
+  if (n == 7) return vsa ? qs_t<7, true>(desc, x, Kocp, maxiter, tol, u) : qs_t<7, false>(desc, x, Kocp, maxiter, tol, u);
+  return -1;
+}
