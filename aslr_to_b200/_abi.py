@@ -113,6 +113,7 @@ _PROTOS = {
                                  C.c_void_p]),
     "aslr_quasi_static": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.c_void_p, C.c_void_p, C.c_int32, C.c_double,
                                     C.c_void_p]),
+    "aslr_shift_warm_start": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "aslr_solver_init": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(SolverOpts), C.POINTER(SolverBuffers),
                                    C.c_void_p]),
     "aslr_solver_calc_diff": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(SolverOpts),

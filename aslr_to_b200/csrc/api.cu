@@ -25,6 +25,22 @@ __global__ void accept_kernel(const SolverArgs a) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b < a.B) accept_body(a, b, a.buf.counters);
 }
+// receding-horizon shift: one thread per (OCP, state/control component) walks the horizon forward, so the
+// in-place move has no read-after-write hazard
+__global__ void shift_kernel(int B, int T, int nx, int nu, double* xs, double* us, const double* x0_new) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  const int per = nx + nu;
+  if (g >= B * per) return;
+  const int b = g / per, i = g % per;
+  if (i < nx) {
+    double* x = xs + (size_t)b * (T + 1) * nx + i;
+    for (int t = 0; t < T; ++t) x[(size_t)t * nx] = x[(size_t)(t + 1) * nx];
+    if (x0_new) x[0] = x0_new[(size_t)b * nx + i];
+  } else {
+    double* u = us + (size_t)b * T * nu + (i - nx);
+    for (int t = 0; t + 1 < T; ++t) u[(size_t)t * nu] = u[(size_t)(t + 1) * nu];
+  }
+}
 }  // namespace
 
 namespace aslr {
@@ -170,6 +186,16 @@ int aslr_quasi_static(const AslrProblem* p, const AslrBatch* batch, const double
   a.B = batch->B, a.T = batch->T, a.xs = xs, a.us = nullptr, a.K_ocp = batch->K_ocp, a.mref_ocp = batch->mref_ocp;
   a.out = AslrKnotOut{};
   if (p->fn.quasi_static(p->dev, a, us, maxiter, tol, (cudaStream_t)stream) != 0) return cuda_fail(cudaGetLastError());
+  return ASLR_OK;
+}
+
+int aslr_shift_warm_start(const AslrProblem* p, const AslrBatch* batch, double* xs, double* us, const double* x0_new,
+                          void* stream) {
+  if (!p || !batch || !xs || !us) return fail(ASLR_ERR_INVALID, "null argument%s");
+  if (batch->B <= 0 || batch->T <= 0) return fail(ASLR_ERR_INVALID, "B and T must be positive%s");
+  const int total = batch->B * (p->nx + p->nu);
+  shift_kernel<<<(total + 127) / 128, 128, 0, (cudaStream_t)stream>>>(batch->B, batch->T, p->nx, p->nu, xs, us, x0_new);
+  if (launch_status()) return cuda_fail(cudaGetLastError());
   return ASLR_OK;
 }
 

@@ -254,6 +254,12 @@ int aslr_calc_diff(const AslrProblem* p, const AslrBatch* batch, const double* x
 int aslr_quasi_static(const AslrProblem* p, const AslrBatch* batch, const double* xs, double* us, int32_t maxiter,
                       double tol, void* stream);
 
+/* Receding-horizon warm start (the MPC loop around examples/two_dof_sea.py:77-81): in place,
+ * xs[t] <- xs[t+1], us[t] <- us[t+1], the last knot is repeated, then xs[0] <- x0_new (optional,
+ * [B][nx]).  The caller also updates batch->x0 before the next aslr_solve. */
+int aslr_shift_warm_start(const AslrProblem* p, const AslrBatch* batch, double* xs, double* us, const double* x0_new,
+                          void* stream);
+
 /* One solver building block each; they operate on the per-OCP state in `buf` exactly like the
  * crocoddyl member functions of the same name. */
 int aslr_solver_init(const AslrProblem* p, const AslrBatch* batch, const AslrSolverOpts* opts,

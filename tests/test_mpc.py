@@ -1,0 +1,56 @@
+"""Receding-horizon loop (BASELINE.json configs[4] pattern): shift + warm-started
+re-solve on the GPU against the oracle solver driven through the same sequence on the CPU."""
+import numpy as np
+import pytest
+
+import oracle_build as ob
+import util as U
+from aslr_to_b200 import workloads as W
+
+crocoddyl = ob.crocoddyl
+
+
+def shift_reference(xs, us, x0_new):
+    xs, us = np.array(xs, float), np.array(us, float)
+    xs[:-1] = xs[1:].copy()
+    us[:-1] = us[1:].copy()
+    xs[0] = x0_new
+    return xs, us
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["sea", "chain7"])
+def test_mpc_steps_match_the_oracle(built_library, name):
+    from aslr_to_b200 import batched as BT, mpc as M
+    rng = np.random.default_rng(11)
+    if name == "sea":
+        w, T, first_iters, step_iters, nsteps = W.sea_batch(3), 30, 30, 4, 3
+    else:
+        w, T, first_iters, step_iters, nsteps = W.chain7_batch(B=2, T=12), 12, 6, 3, 2
+    B = w["x0"].shape[0]
+    prob = BT.BatchedShootingProblem(W.to_desc(w), w["x0"], T, K_ocp=w.get("K_ocp"), mref_ocp=w.get("mref_ocp"))
+    mpc = M.BatchedMPC(prob, W.SOLVER_KIND[w["solver"]], maxiter=step_iters, th_stop=w["th_stop"])
+    xs0, us0 = W.initial_guess(w, w["x0"], T, prob.nu)
+    mpc.initialise(xs0, us0, maxiter=first_iters)
+    # oracle: same first solve, then the same shifts and warm-started solves
+    oracle = []
+    for b in range(B):
+        run, term, x0 = ob.port_models(w, b)
+        problem = crocoddyl.ShootingProblem(x0, [run] * T, term)
+        s = ob.SOLVERS[w["solver"]](problem)
+        s.th_stop = w["th_stop"]
+        s.solve([x0] * (T + 1), [np.zeros(prob.nu)] * T, first_iters)
+        oracle.append((problem, s))
+    assert U.rel_err(mpc.solver.t["xs"].cpu().numpy(), np.array([np.array(s.xs) for _, s in oracle])) <= U.RTOL
+    for step in range(nsteps):
+        x_meas = np.array([np.array(s.xs[1]) for _, s in oracle]) + 1e-2 * rng.standard_normal((B, prob.nx))
+        u0 = mpc.step(x_meas).cpu().numpy()
+        st = mpc.solver.states()
+        for b, (problem, s) in enumerate(oracle):
+            xs, us = shift_reference(np.array(s.xs), np.array(s.us), x_meas[b])
+            problem.x0 = x_meas[b].copy()
+            s.solve(list(xs), list(us), step_iters)
+            assert U.rel_err(mpc.solver.t["xs"][b].cpu().numpy(), np.array(s.xs)) <= 1e-8, (step, b)
+            assert U.rel_err(mpc.solver.t["us"][b].cpu().numpy(), np.array(s.us)) <= 1e-8, (step, b)
+            assert U.rel_err(u0[b], np.array(s.us[0])) <= 1e-8
+            assert abs(st["cost"][b] - s.cost) <= 1e-8 * max(1.0, abs(s.cost))
