@@ -61,7 +61,8 @@ struct AslrProblem {
   Launchers fn;
   // DevProblem<N> for the instantiated N (largest is N = 7)
   alignas(16) unsigned char dev[sizeof(DevProblem<ASLR_MAX_DOF>)];
-  int* pinned_counter;  // host-pinned mirror of counters[0] used by aslr_solve
+  int* pinned_counter;  // host-pinned mirror of counters[0] used by aslr_solve (two poll slots)
+  cudaEvent_t poll_event[2];
 };
 
 extern "C" {
@@ -126,6 +127,7 @@ int aslr_problem_create(const AslrProblemDesc* desc, AslrProblem** out) {
   p->nu = desc->dyn.nu;
   p->vsa = vsa;
   p->pinned_counter = nullptr;
+  p->poll_event[0] = p->poll_event[1] = nullptr;
   std::memset(p->dev, 0, sizeof(p->dev));
   if (n == 2) {
     fill_dev_problem<2>(*desc, *reinterpret_cast<DevProblem<2>*>(p->dev));
@@ -144,6 +146,8 @@ int aslr_problem_create(const AslrProblemDesc* desc, AslrProblem** out) {
 int aslr_problem_destroy(AslrProblem* p) {
   if (p) {
     if (p->pinned_counter) cudaFreeHost(p->pinned_counter);
+    for (int k = 0; k < 2; ++k)
+      if (p->poll_event[k]) cudaEventDestroy(p->poll_event[k]);
     delete p;
   }
   return ASLR_OK;
@@ -266,23 +270,38 @@ int aslr_solve(const AslrProblem* pc, const AslrBatch* batch, const AslrSolverOp
   }
   int launches = 0, it = 0;
   const int poll = opts->poll_every > 0 ? opts->poll_every : 1;
+  if (!p->poll_event[0]) {
+    for (int k = 0; k < 2; ++k) {
+      cudaError_t e = cudaEventCreateWithFlags(&p->poll_event[k], cudaEventDisableTiming);
+      if (e != cudaSuccess) return cuda_fail(e);
+    }
+  }
   if (launch_init(a, s)) return cuda_fail(cudaGetLastError());
   ++launches;
-  p->pinned_counter[0] = batch->B;
-  for (it = 0; it < opts->maxiter; ++it) {
+  // Pipelined polling: the "OCPs still running" word of poll k is read back asynchronously and only
+  // waited for after the iterations up to poll k + 1 have been enqueued, so the GPU never idles on the
+  // host round trip.  A batch that finished costs at most `poll` extra iterations of empty kernels.
+  int pending = -1;  // slot of the poll issued but not yet consumed
+  int n_polls = 0;
+  bool done = false;
+  for (it = 0; it < opts->maxiter && !done; ++it) {
     a.iter = it;
     if (p->fn.calcdiff(p->dev, a, s) || p->fn.backward(p->dev, a, s) || p->fn.rollout(p->dev, a, s) ||
         launch_accept(a, s))
       return cuda_fail(cudaGetLastError());
     launches += 4;
-    if ((it + 1) % poll == 0 || it + 1 == opts->maxiter) {
-      cudaError_t e = cudaMemcpyAsync(p->pinned_counter, buf->counters, sizeof(int), cudaMemcpyDeviceToHost, s);
-      if (e == cudaSuccess) e = cudaStreamSynchronize(s);
-      if (e != cudaSuccess) return cuda_fail(e);
-      if (p->pinned_counter[0] <= 0) {
-        ++it;
-        break;
+    if ((it + 1) % poll == 0 && it + 1 < opts->maxiter) {
+      const int slot = n_polls & 1;
+      if (pending >= 0) {  // consume the previous poll before its slot is reused
+        cudaError_t e = cudaEventSynchronize(p->poll_event[pending]);
+        if (e != cudaSuccess) return cuda_fail(e);
+        if (p->pinned_counter[pending] <= 0) done = true;
       }
+      cudaError_t e = cudaMemcpyAsync(p->pinned_counter + slot, buf->counters, sizeof(int), cudaMemcpyDeviceToHost, s);
+      if (e == cudaSuccess) e = cudaEventRecord(p->poll_event[slot], s);
+      if (e != cudaSuccess) return cuda_fail(e);
+      pending = slot;
+      ++n_polls;
     }
   }
   // adopt the candidates accepted in the last launched iteration (setCandidate)

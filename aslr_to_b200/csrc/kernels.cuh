@@ -10,6 +10,10 @@
 #define ASLR_ROLL_THREADS 64  // 2-DOF rollout: CTA size and minimum resident CTAs per SM (one wave for 40960 trials)
 #define ASLR_ROLL_MINB 5
 #endif
+#ifndef ASLR_BWD_CTA_THREADS
+#define ASLR_BWD_CTA_THREADS 128  // nx = 28 backward pass: threads per OCP and minimum resident CTAs per SM
+#define ASLR_BWD_CTA_MINB 4
+#endif
 #ifndef ASLR_BWD_GS
 #define ASLR_BWD_GS 16  // lanes per OCP in the nx = 8 backward pass
 #endif
@@ -188,7 +192,7 @@ __global__ void __launch_bounds__(GS * GROUPS) backward_warp_kernel(const Solver
 
 // CTA per OCP (nx = 28)
 template <int NX, int NU, int THREADS>
-__global__ void __launch_bounds__(THREADS) backward_cta_kernel(const SolverArgs a, const BoxLimits<NU> lim) {
+__global__ void __launch_bounds__(THREADS, ASLR_BWD_CTA_MINB) backward_cta_kernel(const SolverArgs a, const BoxLimits<NU> lim) {
   extern __shared__ double smem[];
   const int b = blockIdx.x;
   GrpCta<THREADS> g{(int)threadIdx.x};
@@ -261,7 +265,7 @@ struct Launch {
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(per * GROUPS));
       k<<<(a.B + GROUPS - 1) / GROUPS, GS * GROUPS, per * GROUPS, s>>>(a, lim);
     } else {
-      constexpr int THREADS = 128;
+      constexpr int THREADS = ASLR_BWD_CTA_THREADS;
       auto k = backward_cta_kernel<NX, NU, THREADS>;
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)per);
       k<<<a.B, THREADS, per, s>>>(a, lim);

@@ -219,26 +219,6 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
-    if args.kernels:  # per-kernel CUDA-event timings of the first iterations (full batch active)
-        import ctypes as C
-        lib, bs, st = prob.lib, prob.batch_struct(), prob._stream()
-        opts = BT.make_opts(A.SOLVER_FDDP, w["maxiter"], w["th_stop"], lib=lib)
-        solver.t["xs"].copy_(d_xs0), solver.t["us"].copy_(d_us0)
-        A.check(lib.aslr_solver_init(prob.handle, C.byref(bs), C.byref(opts), C.byref(solver.buf), st))
-        rows = []
-        for it in range(args.kernels):
-            row = []
-            for fn, extra in ((lib.aslr_solver_calc_diff, (it,)), (lib.aslr_backward_pass, ()),
-                              (lib.aslr_forward_pass, ()), (lib.aslr_accept_step, (it,))):
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                A.check(fn(prob.handle, C.byref(bs), C.byref(opts), C.byref(solver.buf), *extra, st))
-                e1.record()
-                torch.cuda.synchronize()
-                row.append(round(e0.elapsed_time(e1) * 1e3, 1))
-            rows.append(row)
-        print(json.dumps({"kernel_us_per_iteration[calcdiff,backward,rollout,accept]": rows}))
-        return
     if args.profile:  # for ncu: one warm-up solve, one profiled solve, nothing else
         step_device()
         torch.cuda.synchronize()
@@ -324,6 +304,90 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_chain7_mpc(args):
+    """Secondary workload (BASELINE.json configs[4]): 1024 x 7-link SEA arm (nx = 28), T = 200.  One untimed
+    solve to (near) convergence, then timed MPC steps: shift the solution by one knot, perturb x0 by N(0, 1e-2)
+    and re-solve with maxiter = 10 from the warm start.  Single GPU; prints its own JSON line."""
+    import torch
+    from aslr_to_b200 import _abi as A, batched as BT, mpc as M, workloads as W
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the product path")
+    torch.cuda.set_device(0)
+    B, T = args.chain7_ocps, 200
+    w = W.chain7_batch(B=B, T=T)
+    prob = BT.BatchedShootingProblem(W.to_desc(w), w["x0"], T, mref_ocp=w["mref_ocp"])
+    mpc = M.BatchedMPC(prob, A.SOLVER_FDDP, maxiter=10, th_stop=w["th_stop"], store_log=False)
+    xs0, us0 = W.initial_guess(w, w["x0"], T, prob.nu)
+    t0 = time.perf_counter()
+    first = mpc.initialise(xs0, us0, maxiter=100)
+    torch.cuda.synchronize()
+    first_s = time.perf_counter() - t0
+    st0 = first.states()
+    rng = np.random.default_rng(5)
+    noise = [torch.as_tensor(1e-2 * rng.standard_normal((B, prob.nx)), device=prob.device)
+             for _ in range(args.warmup + args.steps)]
+    iters = 0
+
+    def one(k):
+        x_meas = mpc.solver.t["xs"][:, 1, :] + noise[k]
+        mpc.step(x_meas)
+        st = mpc.solver.states()
+        return int(np.sum(st["iter"] + (st["status"] == A.OCP_CONVERGED)))
+    for k in range(args.warmup):
+        one(k)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for k in range(args.steps):
+        iters += one(args.warmup + k)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    print(json.dumps({
+        "metric": "batched_fddp_ocp_iters_per_s", "value": iters / (ms * 1e-3), "unit": UNIT, "n_gpus": 1,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "%d x 7-link SEA arm MPC warm-start steps (BASELINE.json configs[4]), T=200, nx=28, "
+                               "maxiter=10 per step" % B, "ocps": B, "T": T, "nx": 28, "nu": 7},
+        "first_solve_s": first_s, "first_solve_converged": int(np.sum(st0["status"] == A.OCP_CONVERGED)),
+        "first_solve_iters": int(np.sum(st0["iter"])), "ocp_iters_per_step": iters / args.steps,
+        "gpu_launches": int(mpc.solver.result.kernel_launches) * args.steps}))
+
+
+def run_kernel_times(args):
+    """--kernels N: CUDA-event time of each solver kernel in the first N iterations (full batch active)."""
+    import ctypes as C
+    import torch
+    from aslr_to_b200 import _abi as A, batched as BT, workloads as W
+    torch.cuda.set_device(0)
+    if args.workload == "chain7_mpc":
+        w = W.chain7_batch(B=args.chain7_ocps, T=200)
+        prob = BT.BatchedShootingProblem(W.to_desc(w), w["x0"], 200, mref_ocp=w["mref_ocp"])
+    else:
+        w = W.sea_batch(B_PER_GPU, seed=SEED)
+        prob = BT.BatchedShootingProblem(W.to_desc(w), w["x0"], w["T"], K_ocp=w["K_ocp"])
+    solver = BT.BatchedSolver(prob, A.SOLVER_FDDP, maxiter=w["maxiter"], th_stop=w["th_stop"], store_vxx=False,
+                              store_quu=False, store_log=False)
+    xs0, us0 = W.initial_guess(w, np.asarray(w["x0"]), prob.T, prob.nu)
+    solver.set_candidate(xs0, us0)
+    lib, bs, st = prob.lib, prob.batch_struct(), prob._stream()
+    opts = BT.make_opts(A.SOLVER_FDDP, w["maxiter"], w["th_stop"], lib=lib)
+    A.check(lib.aslr_solver_init(prob.handle, C.byref(bs), C.byref(opts), C.byref(solver.buf), st))
+    rows = []
+    for it in range(args.kernels):
+        row = []
+        for fn, extra in ((lib.aslr_solver_calc_diff, (it,)), (lib.aslr_backward_pass, ()),
+                          (lib.aslr_forward_pass, ()), (lib.aslr_accept_step, (it,))):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            A.check(fn(prob.handle, C.byref(bs), C.byref(opts), C.byref(solver.buf), *extra, st))
+            e1.record()
+            torch.cuda.synchronize()
+            row.append(round(e0.elapsed_time(e1) * 1e3, 1))
+        rows.append(row)
+    print(json.dumps({"workload": args.workload, "kernel_us_per_iteration[calcdiff,backward,rollout,accept]": rows}))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -334,8 +398,14 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--kernels", type=int, default=0, help="time each kernel of the first N iterations")
     ap.add_argument("--profile", action="store_true", help="two solves only (for ncu launch lists)")
+    ap.add_argument("--workload", default="sea4096", choices=["sea4096", "chain7_mpc"])
+    ap.add_argument("--chain7-ocps", type=int, default=1024)
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.kernels:
+        run_kernel_times(args)
+    elif args.workload == "chain7_mpc":
+        run_chain7_mpc(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)
