@@ -151,7 +151,7 @@ def run_reference(args):
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from aslr_to_b200 import _abi as A, batched as BT, workloads as W
+    from aslr_to_b200 import _abi as A, batched as BT, sharding as S, workloads as W
     initial_guess_arrays = W.initial_guess
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -177,18 +177,13 @@ def run_ours(args):
     h_xs = torch.empty((B, T + 1, nx), dtype=torch.float64).pin_memory()
     h_us = torch.empty((B, T, nu), dtype=torch.float64).pin_memory()
     h_state = torch.empty((B, A.OCP_STATE_DOUBLES), dtype=torch.float64).pin_memory()
-    gather = None
-    if world > 1:
-        gather = {k: torch.empty((world,) + tuple(solver.t[k].shape), dtype=torch.float64, device=dev)
-                  for k in ("xs", "us", "state")}
 
     def step_device():
         solver.t["xs"].copy_(d_xs0)
         solver.t["us"].copy_(d_us0)
         solver.solve(set_candidate=False)
         if world > 1:  # the only collective of the path: final gather of costs / iterations / trajectories
-            for k in ("xs", "us", "state"):
-                dist.all_gather_into_tensor(gather[k], solver.t[k])
+            S.gather_results({k: solver.t[k] for k in ("xs", "us", "state")}, B * world)
 
     def step_e2e():
         prob.x0.copy_(h_x0, non_blocking=True)
