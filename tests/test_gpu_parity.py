@@ -184,3 +184,48 @@ def test_missing_device_pointers_are_rejected(BT):
     o = BT.make_opts(A.SOLVER_FDDP, 3)
     rc = prob.lib.aslr_solve(prob.handle, C.byref(b), C.byref(o), C.byref(buf), None, None)
     assert rc == -1 and b"null" in prob.lib.aslr_last_error()
+
+
+@pytest.mark.parametrize("B,T", [(1, 1), (5, 3), (37, 7), (130, 2)])
+def test_ragged_batch_sizes_match_the_host_build(BT, hostmath, B, T):
+    """Batch / horizon sizes that are not multiples of the warp, of the K1 staging tile, of the 8 OCPs per
+    K2 CTA or of the rollout CTA: every knot record of the fused sweep and a short solve against the g++
+    build of the same device code."""
+    from util import host_knot, host_solve
+    w = W.sea_batch(B, seed=99)
+    w["T"], w["maxiter"] = T, 3
+    desc = W.to_desc(w)
+    rng = np.random.default_rng(B * 100 + T)
+    xs = rng.uniform(-1, 1, (B, T + 1, 8))
+    us = rng.uniform(-1, 1, (B, T, 2))
+    prob = BT.BatchedShootingProblem(desc, w["x0"], T, K_ocp=w["K_ocp"])
+    out = prob.calc_diff(xs, us, want=("xnext", "cost", "deriv"))
+    rec = prob.split_record(out["deriv"].cpu().numpy())
+    cost, xnext = out["cost"].cpu().numpy(), out["xnext"].cpu().numpy()
+    for b in sorted(set([0, B // 2, B - 1])):
+        for t in range(T + 1):
+            h = host_knot(hostmath, desc, xs[b, t], None if t == T else us[b, t], terminal=(t == T), Kocp=w["K_ocp"][b])
+            for k in ("Fx", "Fu", "Lx", "Lu", "Lxx", "Luu"):
+                assert rel_err(rec[k][b, t], h[k]) < 1e-12, (b, t, k)
+            assert abs(cost[b, t] - h["cost"]) <= 1e-12 * max(1.0, abs(h["cost"]))
+            if t < T:
+                assert rel_err(xnext[b, t], h["xnext"]) < 1e-12
+    res = gpu_solve(BT, w, T=T)
+    ref = host_solve(hostmath, w, T=T)
+    assert np.array_equal(res["states"]["iter"], ref["states"]["iter"])
+    assert np.array_equal(res["states"]["status"], ref["states"]["status"])
+    assert rel_err(res["xs"], ref["xs"]) < 1e-9 and rel_err(res["us"], ref["us"]) < 1e-9
+    assert rel_err(res["states"]["cost"], ref["states"]["cost"]) < 1e-9
+
+
+def test_empty_batch_is_a_no_op(BT):
+    w = W.two_dof_sea()
+    prob = BT.BatchedShootingProblem(W.to_desc(w), np.zeros((1, 8)), 4)
+    prob.B = 0  # an empty shard (B % world ranks can leave a rank without OCPs)
+    import torch
+    out = BT.A.KnotOut()
+    b = prob.batch_struct()
+    dummy = torch.zeros(8, dtype=torch.float64, device=prob.device)
+    import ctypes as C
+    BT.A.check(prob.lib.aslr_calc_diff(prob.handle, C.byref(b), dummy.data_ptr(), None, C.byref(out), prob._stream()))
+    torch.cuda.synchronize()
