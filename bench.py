@@ -33,6 +33,7 @@ METRIC = "batched_fddp_ocp_iters_per_s"
 UNIT = "OCP-iterations/s"
 B_PER_GPU = 4096
 SEED = 20240001
+K1_DRAM_TRAFFIC_PER_LAUNCH = 773.4e6  # dram__bytes_read + write of one knot_kernel launch, ncu --set full (profiles/r01b_ncu_full.md)
 ALGO_BYTES_PER_KNOT = 1544  # 2-DOF SEA, read x,u; write xnext,cost,Fx,Fu,Lx,Lu,Lxx,Lxu,Luu
 
 
@@ -286,7 +287,10 @@ def run_ours(args):
             "roofline": {"kernel": "knot_kernel<2,2,SEA,DIFF> (fused calc+calcDiff, %d knots)" % knots,
                          "bound": "hbm", "achieved": achieved, "peak": peak,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None},
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": K1_DRAM_TRAFFIC_PER_LAUNCH,
+                         "traffic_source": "ncu --set full capture of this kernel, profiles/r01b_ncu_full.md",
+                         "fp64": {"dfma_latency_cycles": 8.2, "peak_tflops_measured": 34.2,
+                                  "source": "tools/fp64_peak.cu on this pool, profiles/r01b_fp64_peak.json"}},
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu:
