@@ -10,6 +10,9 @@
 #define ASLR_ROLL_THREADS 64  // 2-DOF rollout: CTA size and minimum resident CTAs per SM (one wave for 40960 trials)
 #define ASLR_ROLL_MINB 5
 #endif
+#ifndef ASLR_K1_MINB
+#define ASLR_K1_MINB 2  // 2-DOF calc+calcDiff: minimum resident CTAs per SM (register cap 65536 / (128 * MINB))
+#endif
 #ifndef ASLR_BWD_CTA_THREADS
 #define ASLR_BWD_CTA_THREADS 128  // nx = 28 backward pass: threads per OCP and minimum resident CTAs per SM
 #define ASLR_BWD_CTA_MINB 4
@@ -46,13 +49,28 @@ struct RecParts {
 template <int SIZE, int LO, int LEN>
 __device__ __forceinline__ void flush_part(const double* st, double* deriv, long g0, unsigned mask, int lane) {
   constexpr int HI = (LO + LEN < SIZE) ? LO + LEN : SIZE;
+  constexpr int N = HI - LO, PER = (N + 31) / 32, RB = 8;  // RB records per batch: RB * PER loads in flight
   __syncwarp();
-#pragma unroll 4
-  for (int r = 0; r < 32; ++r) {
-    if (!((mask >> r) & 1u)) continue;
-    double* o = deriv + (size_t)(g0 + r) * SIZE + LO;
 #pragma unroll
-    for (int e = lane; e < HI - LO; e += 32) o[e] = st[e * RecParts<SIZE>::STRIDE + r];
+  for (int r0 = 0; r0 < 32; r0 += RB) {
+    double v[RB][PER];
+#pragma unroll
+    for (int i = 0; i < RB; ++i)
+#pragma unroll
+      for (int h = 0; h < PER; ++h) {
+        const int e = lane + 32 * h;
+        v[i][h] = (e < N) ? st[e * RecParts<SIZE>::STRIDE + r0 + i] : 0.0;
+      }
+#pragma unroll
+    for (int i = 0; i < RB; ++i) {
+      if (!((mask >> (r0 + i)) & 1u)) continue;
+      double* o = deriv + (size_t)(g0 + r0 + i) * SIZE + LO;
+#pragma unroll
+      for (int h = 0; h < PER; ++h) {
+        const int e = lane + 32 * h;
+        if (e < N) o[e] = v[i][h];
+      }
+    }
   }
   __syncwarp();
 }
@@ -72,7 +90,7 @@ __device__ __forceinline__ void staged_record(double* st, double* deriv, long g0
 
 // stand-alone calc / calc+calcDiff sweep: one thread per knot (ShootingProblem.calc / calcDiff)
 template <int N, int NU, bool VSA, bool DIFF>
-__global__ void __launch_bounds__(128) knot_kernel(const __grid_constant__ DevProblem<N> P, const KnotArgs a) {
+__global__ void __launch_bounds__(128, (N <= 2) ? ASLR_K1_MINB : 1) knot_kernel(const __grid_constant__ DevProblem<N> P, const KnotArgs a) {
   constexpr int NX = 4 * N;
   typedef Rec<NX, NU> RC;
   constexpr bool STAGED = DIFF && (N <= 2);
@@ -126,7 +144,7 @@ __global__ void __launch_bounds__(128) knot_kernel(const __grid_constant__ DevPr
 
 // ------------------------------------------------------------------------------- solver kernels
 template <int N, int NU, bool VSA>
-__global__ void __launch_bounds__(128) solver_calcdiff_kernel(const __grid_constant__ DevProblem<N> P,
+__global__ void __launch_bounds__(128, (N <= 2) ? ASLR_K1_MINB : 1) solver_calcdiff_kernel(const __grid_constant__ DevProblem<N> P,
                                                               const SolverArgs a) {
   typedef Rec<4 * N, NU> RC;
   extern __shared__ double stage[];
