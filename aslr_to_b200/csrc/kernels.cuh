@@ -174,6 +174,28 @@ __global__ void __launch_bounds__((N <= 2) ? ASLR_ROLL_THREADS : 64, (N <= 2) ? 
   rollout_body<N, NU, VSA>(P, a, (int)(g / ASLR_NUM_ALPHAS), (int)(g % ASLR_NUM_ALPHAS));
 }
 
+// K3b: one warp per trial; lanes take the knots 32 at a time, the costs are then added in knot order
+// (shuffle broadcast, every lane keeps the same running total) so the sum equals the sequential one.
+template <int N, int NU, bool VSA>
+__global__ void __launch_bounds__(128) trial_cost_kernel(const __grid_constant__ DevProblem<N> P, const SolverArgs a,
+                                                         const int pass) {
+  // pass 0: alpha = 1 of every OCP (and its acceptance test); pass 1: the other nine, where still needed
+  const int per = pass == 0 ? 1 : ASLR_NUM_ALPHAS - 1;
+  const long w = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= (long)a.B * per) return;
+  const int b = (int)(w / per), ai = pass == 0 ? 0 : 1 + (int)(w % per);
+  if (!trial_cost_wanted(a, b, ai)) return;
+  double total = 0.0;
+  for (int base = 0; base <= a.T; base += 32) {
+    const int t = base + lane;
+    const double c = (t <= a.T) ? trial_knot_cost<N, NU, VSA>(P, a, b, ai, t) : 0.0;
+    const int n = (a.T + 1 - base < 32) ? a.T + 1 - base : 32;
+    for (int l = 0; l < n; ++l) total += __shfl_sync(0xffffffffu, c, l);
+  }
+  if (lane == 0) trial_cost_finish(a, b, ai, total);
+}
+
 // quasiStatic of every running knot: one thread per (OCP, knot)
 template <int N, int NU, bool VSA>
 __global__ void __launch_bounds__(64) quasi_static_kernel(const __grid_constant__ DevProblem<N> P, const KnotArgs a,
@@ -269,6 +291,10 @@ struct Launch {
     const long total = (long)a.B * ASLR_NUM_ALPHAS;
     const int threads = (N <= 2) ? ASLR_ROLL_THREADS : 64;
     rollout_kernel<N, NU, VSA><<<(unsigned)((total + threads - 1) / threads), threads, 0, s>>>(P, a);
+    if (launch_status()) return -2;
+    trial_cost_kernel<N, NU, VSA><<<(unsigned)(((long)a.B * 32 + 127) / 128), 128, 0, s>>>(P, a, 0);
+    trial_cost_kernel<N, NU, VSA>
+        <<<(unsigned)(((long)a.B * (ASLR_NUM_ALPHAS - 1) * 32 + 127) / 128), 128, 0, s>>>(P, a, 1);
     return launch_status();
   }
   static int backward(const void* Pv, const SolverArgs& a, cudaStream_t s) {

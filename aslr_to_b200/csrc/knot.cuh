@@ -36,6 +36,121 @@ struct CostAcc {
 // Y_i-derivative applied to a motion m:  (S x* (Y m)) - Y (S x m), with Ym = Y m precomputed
 ASLR_HD SV dY_mul(const SI& Y, SV S, SV m, SV Ym) { return cross_mf(S, Ym) - mul(Y, cross_mm(S, m)); }
 
+// crocoddyl.CostModelSum over the term menu: returns the cost; with DIFF also accumulates the derivative
+// sums into `acc`.  R, p: world poses of the joints; S: world-frame joint axes (DIFF only, may be null).
+template <int N, int NU, bool DIFF>
+ASLR_HD double cost_terms(const DevCostSum<N>& C, const double* x, const double* u, const M3* R, const V3* p, const SV* S,
+                          const double* mref, CostAcc<N>& acc) {
+  constexpr int NX = 4 * N;
+  double cost = 0.0;
+#pragma unroll 1
+  for (int k = 0; k < C.nterms; ++k) {
+    const DevCostTerm<N>& t = C.t[k];
+    const double w = t.weight;
+    if (t.kind == ASLR_COST_FRAME_PLACEMENT) {
+      // residual_frame_placement.py:13-24
+      M3 Rp = R[0];
+      V3 pp = p[0];
+#pragma unroll
+      for (int i = 1; i < N; ++i)
+        if (i == t.frame_parent) Rp = R[i], pp = p[i];
+      const M3 Rf = mul(Rp, ldm3(t.fR));
+      const V3 pf = pp + mul(Rp, ld3(t.fp));
+      const double* rf = mref ? mref : t.ref;
+      const M3 Rref = ldm3(rf);
+      const M3 Rr = mulTN(Rref, Rf);
+      const V3 pr = mulT(Rref, pf - ld3(rf + 9));
+      double r[6], theta;
+      V3 wv;
+      se3_log(Rr, pr, r, wv, theta);
+      double c = 0;
+#pragma unroll
+      for (int i = 0; i < 6; ++i) c += t.act[i] * r[i] * r[i];
+      cost += w * (0.5 * c);
+      if (DIFF) {
+        M3 A, CA;
+        se3_jlog(wv, theta, pr, A, CA);
+        double J[6 * N];
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const bool on = (j <= t.frame_parent);
+          const V3 ang = mulT(Rf, S[j].a);
+          const V3 lin = mulT(Rf, S[j].l + cross(S[j].a, pf));
+          const V3 jl = mul(A, lin) + mul(CA, ang);
+          const V3 ja = mul(A, ang);
+          J[0 * N + j] = on ? jl.x : 0.0, J[1 * N + j] = on ? jl.y : 0.0, J[2 * N + j] = on ? jl.z : 0.0;
+          J[3 * N + j] = on ? ja.x : 0.0, J[4 * N + j] = on ? ja.y : 0.0, J[5 * N + j] = on ? ja.z : 0.0;
+        }
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+          double g = 0;
+#pragma unroll
+          for (int m = 0; m < 6; ++m) g += J[m * N + i] * (t.act[m] * r[m]);
+          acc.Lx[i] += w * g;
+#pragma unroll
+          for (int j = 0; j < N; ++j) {
+            double h = 0;
+#pragma unroll
+            for (int m = 0; m < 6; ++m) h += J[m * N + i] * (t.act[m] * J[m * N + j]);
+            acc.Lqq[i * N + j] += w * h;
+          }
+        }
+      }
+    } else if (t.kind == ASLR_COST_STATE) {
+      // ResidualModelState: r = diff(xref, x) = x - xref; weighted-quad activation
+      double c = 0;
+#pragma unroll
+      for (int i = 0; i < NX; ++i) {
+        const double r = x[i] - t.ref[i];
+        c += t.act[i] * r * r;
+        if (DIFF) acc.Lx[i] += w * (t.act[i] * r), acc.Lxxd[i] += w * t.act[i];
+      }
+      cost += w * (0.5 * c);
+    } else if (t.kind == ASLR_COST_CONTROL) {
+      double c = 0;
+#pragma unroll
+      for (int i = 0; i < NU; ++i) {
+        const double r = u[i] - t.ref[i];
+        c += t.act[i] * r * r;
+        if (DIFF) acc.Lu[i] += w * (t.act[i] * r), acc.Luud[i] += w * t.act[i];
+      }
+      cost += w * (0.5 * c);
+    } else if (t.kind == ASLR_COST_STIFFNESS) {
+      // linear cost sum(lamda (sigma - sigma_ref)), stiffness_cost.py:13-20
+      double c = 0;
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        if (NU > N) c += t.act[0] * (u[(NU > N ? N : 0) + i] - t.ref[i]);
+        if (DIFF && NU > N) acc.Lu[(NU > N ? N : 0) + i] += w * t.act[0];
+      }
+      cost += w * c;
+    } else if (t.kind == ASLR_COST_DOUBLE_PENDULUM) {
+      // python/aslr_to/__init__.py:229-249 (n = 2 only; checked at problem creation)
+      if (N == 2) {
+        double s1, c1, s2, c2;
+        sincos(x[0], &s1, &c1);
+        sincos(x[1], &s2, &c2);
+        const double r0 = s1, r1 = s2, r2 = 1 + c1, r3 = 1 + c2, r4 = x[NX > 4 ? 4 : 0], r5 = x[NX > 5 ? 5 : 0];
+        const double* aw = t.act;
+        cost += w * (0.5 * (aw[0] * r0 * r0 + aw[1] * r1 * r1 + aw[2] * r2 * r2 + aw[3] * r3 * r3 + aw[4] * r4 * r4 +
+                            aw[5] * r5 * r5));
+        if (DIFF) {
+          acc.Lx[0] += w * (c1 * (aw[0] * r0) - s1 * (aw[2] * r2));
+          acc.Lx[1] += w * (c2 * (aw[1] * r1) - s2 * (aw[3] * r3));
+          acc.Lx[NX > 4 ? 4 : 0] += w * (aw[4] * r4);
+          acc.Lx[NX > 5 ? 5 : 0] += w * (aw[5] * r5);
+          // the reference's diagonal pseudo-Hessian (from the 1 - cos variant), reproduced verbatim
+          acc.Lxxd[0] += w * ((c1 * c1 - s1 * s1) * aw[0] + (s1 * s1 + (1 - c1) * c1) * aw[2]);
+          acc.Lxxd[1] += w * ((c2 * c2 - s2 * s2) * aw[1] + (s2 * s2 + (1 - c2) * c2) * aw[3]);
+          acc.Lxxd[NX > 4 ? 4 : 0] += w * aw[4];
+          acc.Lxxd[NX > 5 ? 5 : 0] += w * aw[5];
+        }
+      }
+    }
+  }
+  return cost;
+}
+
 // What calcDiff leaves behind for the record: the differential model's Jacobians and the cost sums.
 template <int N, int NU>
 struct KnotDeriv {
@@ -45,7 +160,8 @@ struct KnotDeriv {
 };
 
 // calc (+ calcDiff up to the differential-model Jacobians and cost derivatives, left in `kd`)
-template <int N, int NU, bool VSA, bool DIFF>
+// COSTS = false: dynamics only (the x-chain of the trial rollout); cost_out is left at 0.
+template <int N, int NU, bool VSA, bool DIFF, bool COSTS = true>
 ASLR_HD void knot_core(const DevProblem<N>& P, const DevCostSum<N>& C, const double dt, const double* x,
                        const double* u, const double* Kocp, const double* mref, double* xnext, double& cost_out,
                        KnotDeriv<N, NU>& kd, double* xout, double* dFx, double* dFu) {
@@ -202,111 +318,7 @@ ASLR_HD void knot_core(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
 #pragma unroll
     for (int i = 0; i < N * N; ++i) acc.Lqq[i] = 0;
   }
-#pragma unroll 1
-  for (int k = 0; k < C.nterms; ++k) {
-    const DevCostTerm<N>& t = C.t[k];
-    const double w = t.weight;
-    if (t.kind == ASLR_COST_FRAME_PLACEMENT) {
-      // residual_frame_placement.py:13-24
-      M3 Rp = R[0];
-      V3 pp = p[0];
-#pragma unroll
-      for (int i = 1; i < N; ++i)
-        if (i == t.frame_parent) Rp = R[i], pp = p[i];
-      const M3 Rf = mul(Rp, ldm3(t.fR));
-      const V3 pf = pp + mul(Rp, ld3(t.fp));
-      const double* rf = mref ? mref : t.ref;
-      const M3 Rref = ldm3(rf);
-      const M3 Rr = mulTN(Rref, Rf);
-      const V3 pr = mulT(Rref, pf - ld3(rf + 9));
-      double r[6], theta;
-      V3 wv;
-      se3_log(Rr, pr, r, wv, theta);
-      double c = 0;
-#pragma unroll
-      for (int i = 0; i < 6; ++i) c += t.act[i] * r[i] * r[i];
-      cost += w * (0.5 * c);
-      if (DIFF) {
-        M3 A, CA;
-        se3_jlog(wv, theta, pr, A, CA);
-        double J[6 * N];
-#pragma unroll
-        for (int j = 0; j < N; ++j) {
-          const bool on = (j <= t.frame_parent);
-          const V3 ang = mulT(Rf, S[j].a);
-          const V3 lin = mulT(Rf, S[j].l + cross(S[j].a, pf));
-          const V3 jl = mul(A, lin) + mul(CA, ang);
-          const V3 ja = mul(A, ang);
-          J[0 * N + j] = on ? jl.x : 0.0, J[1 * N + j] = on ? jl.y : 0.0, J[2 * N + j] = on ? jl.z : 0.0;
-          J[3 * N + j] = on ? ja.x : 0.0, J[4 * N + j] = on ? ja.y : 0.0, J[5 * N + j] = on ? ja.z : 0.0;
-        }
-#pragma unroll
-        for (int i = 0; i < N; ++i) {
-          double g = 0;
-#pragma unroll
-          for (int m = 0; m < 6; ++m) g += J[m * N + i] * (t.act[m] * r[m]);
-          acc.Lx[i] += w * g;
-#pragma unroll
-          for (int j = 0; j < N; ++j) {
-            double h = 0;
-#pragma unroll
-            for (int m = 0; m < 6; ++m) h += J[m * N + i] * (t.act[m] * J[m * N + j]);
-            acc.Lqq[i * N + j] += w * h;
-          }
-        }
-      }
-    } else if (t.kind == ASLR_COST_STATE) {
-      // ResidualModelState: r = diff(xref, x) = x - xref; weighted-quad activation
-      double c = 0;
-#pragma unroll
-      for (int i = 0; i < NX; ++i) {
-        const double r = x[i] - t.ref[i];
-        c += t.act[i] * r * r;
-        if (DIFF) acc.Lx[i] += w * (t.act[i] * r), acc.Lxxd[i] += w * t.act[i];
-      }
-      cost += w * (0.5 * c);
-    } else if (t.kind == ASLR_COST_CONTROL) {
-      double c = 0;
-#pragma unroll
-      for (int i = 0; i < NU; ++i) {
-        const double r = u[i] - t.ref[i];
-        c += t.act[i] * r * r;
-        if (DIFF) acc.Lu[i] += w * (t.act[i] * r), acc.Luud[i] += w * t.act[i];
-      }
-      cost += w * (0.5 * c);
-    } else if (t.kind == ASLR_COST_STIFFNESS) {
-      // linear cost sum(lamda (sigma - sigma_ref)), stiffness_cost.py:13-20
-      double c = 0;
-#pragma unroll
-      for (int i = 0; i < N; ++i) {
-        if (NU > N) c += t.act[0] * (u[(NU > N ? N : 0) + i] - t.ref[i]);
-        if (DIFF && NU > N) acc.Lu[(NU > N ? N : 0) + i] += w * t.act[0];
-      }
-      cost += w * c;
-    } else if (t.kind == ASLR_COST_DOUBLE_PENDULUM) {
-      // python/aslr_to/__init__.py:229-249 (n = 2 only; checked at problem creation)
-      if (N == 2) {
-        double s1, c1, s2, c2;
-        sincos(x[0], &s1, &c1);
-        sincos(x[1], &s2, &c2);
-        const double r0 = s1, r1 = s2, r2 = 1 + c1, r3 = 1 + c2, r4 = x[NX > 4 ? 4 : 0], r5 = x[NX > 5 ? 5 : 0];
-        const double* aw = t.act;
-        cost += w * (0.5 * (aw[0] * r0 * r0 + aw[1] * r1 * r1 + aw[2] * r2 * r2 + aw[3] * r3 * r3 + aw[4] * r4 * r4 +
-                            aw[5] * r5 * r5));
-        if (DIFF) {
-          acc.Lx[0] += w * (c1 * (aw[0] * r0) - s1 * (aw[2] * r2));
-          acc.Lx[1] += w * (c2 * (aw[1] * r1) - s2 * (aw[3] * r3));
-          acc.Lx[NX > 4 ? 4 : 0] += w * (aw[4] * r4);
-          acc.Lx[NX > 5 ? 5 : 0] += w * (aw[5] * r5);
-          // the reference's diagonal pseudo-Hessian (from the 1 - cos variant), reproduced verbatim
-          acc.Lxxd[0] += w * ((c1 * c1 - s1 * s1) * aw[0] + (s1 * s1 + (1 - c1) * c1) * aw[2]);
-          acc.Lxxd[1] += w * ((c2 * c2 - s2 * s2) * aw[1] + (s2 * s2 + (1 - c2) * c2) * aw[3]);
-          acc.Lxxd[NX > 4 ? 4 : 0] += w * aw[4];
-          acc.Lxxd[NX > 5 ? 5 : 0] += w * aw[5];
-        }
-      }
-    }
-  }
+  if (COSTS) cost = cost_terms<N, NU, DIFF>(C, x, u, R, p, S, mref, acc);
   cost_out = cost;  // NOT scaled by dt (integrated_action.py:19)
   if (!DIFF) return;
 
@@ -503,6 +515,33 @@ ASLR_HD void record_put(double* rec, const int stride, const double dt, const Kn
   }
 }
 #undef ASLR_PUT
+
+// Cost of one knot without the dynamics (forward kinematics + cost terms only): the per-knot work of the
+// trial-cost kernel.  The kinematics are the statements of knot_core, so the poses are identical.
+template <int N, int NU>
+ASLR_HD double knot_cost_only(const DevProblem<N>& P, const DevCostSum<N>& C, const double* x, const double* u,
+                              const double* mref) {
+  M3 R[N];
+  V3 p[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    double s, c;
+    sincos(x[i], &s, &c);
+    const double omc = 1.0 - c;
+    M3 Rl;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) Rl.m[k] = P.j[i].A0[k] + s * P.j[i].A1[k] + omc * P.j[i].A2[k];
+    if (i == 0) {
+      R[0] = Rl;
+      p[0] = ld3(P.j[0].p);
+    } else {
+      R[i] = mul(R[i - 1], Rl);
+      p[i] = p[i - 1] + mul(R[i - 1], ld3(P.j[i].p));
+    }
+  }
+  CostAcc<N> unused;
+  return cost_terms<N, NU, false>(C, x, u, R, p, nullptr, mref, unused);
+}
 
 // knot_core + the whole record written straight to `rec` (contiguous)
 template <int N, int NU, bool VSA, bool DIFF>

@@ -288,8 +288,8 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
       ut[t * NU + j] = uj;
     }
     double c;
-    knot_eval<N, NU, VSA, false>(P, P.run, P.dt, x, u, Kocp, mref, xn, c, nullptr, nullptr, nullptr, nullptr);
-    cost_try += c;
+    KnotDeriv<N, NU> unused;
+    knot_core<N, NU, VSA, false, false>(P, P.run, P.dt, x, u, Kocp, mref, xn, c, unused, nullptr, nullptr, nullptr);
     double xmax = 0.0;
     bool xnan = false;
 #pragma unroll
@@ -298,7 +298,7 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
       xnan = xnan || isnan(xn[i]);
       x[i] = xn[i];
     }
-    if (bad_value(cost_try) || xnan || bad_value(xmax)) {
+    if (xnan || bad_value(xmax)) {
       ok = false;
       break;
     }
@@ -310,17 +310,89 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
       xt[T * NX + i] = x[i];
       if (need_dv) dv += wv[T * NX + i] * (x[i] - xs[T * NX + i]);
     }
-#pragma unroll
-    for (int j = 0; j < NU; ++j) u[j] = P.u_none[j];
-    double c;
-    knot_eval<N, NU, VSA, false>(P, P.term, P.dtT, x, u, Kocp, mref, xn, c, nullptr, nullptr, nullptr, nullptr);
-    cost_try += c;
-    if (bad_value(cost_try)) ok = false;
   }
-  tr[0] = cost_try;
+  tr[0] = 0.0;  // filled by the trial-cost pass
   tr[1] = dv;
   tr[2] = ok ? 1.0 : 0.0;
   tr[3] = 0.0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3b: cost of the trial trajectories.  The costs do not feed the state recursion, so they are taken off
+// the sequential chain (a third of its instructions) and evaluated for all (OCP, alpha, knot) in parallel;
+// the per-trial total is then accumulated in knot order, as the sequential forwardPass does, so that
+// cost_try is the same floating-point sum.  trial_knot_cost = cost of knot t of trial (b, ai);
+// trial_cost_finish = what the caller does with the ordered total.
+// ---------------------------------------------------------------------------------------------
+template <int N, int NU, bool VSA>
+ASLR_HD double trial_knot_cost(const DevProblem<N>& P, const SolverArgs& a, int b, int ai, int t) {
+  constexpr int NX = 4 * N;
+  const int T = a.T;
+  const double* mref = a.mref_ocp ? a.mref_ocp + (size_t)b * 12 : nullptr;
+  const double* xp = a.buf.xs_try + (((size_t)b * ASLR_NUM_ALPHAS + ai) * (T + 1) + t) * NX;
+  double x[NX], u[NU];
+#pragma unroll
+  for (int i = 0; i < NX; ++i) x[i] = xp[i];
+  if (t < T) {
+    const double* up = a.buf.us_try + (((size_t)b * ASLR_NUM_ALPHAS + ai) * T + t) * NU;
+#pragma unroll
+    for (int i = 0; i < NU; ++i) u[i] = up[i];
+  } else {
+#pragma unroll
+    for (int i = 0; i < NU; ++i) u[i] = P.u_none[i];
+  }
+  return knot_cost_only<N, NU>(P, t < T ? P.run : P.term, x, u, mref);
+}
+
+// Acceptance test of SolverDDP::solve / SolverFDDP::solve for one trial (Appendix A.1): fills dV, d1, d2, dVexp
+// and says whether the step is taken.  Pure function of the OCP state and the trial record, shared by the
+// line-search kernel and by the lazy trial-cost pass (which only needs to know whether alpha = 1 is taken).
+struct TrialTest {
+  double dV, d1, d2, dVexp;
+  bool accept;
+};
+ASLR_HD TrialTest trial_accept_test(const AslrOcpState& s, const AslrSolverOpts& o, int ai, const double* tr) {
+  const double alpha = 1.0 / (double)(1 << ai);
+  const bool fddp = (o.kind == ASLR_SOLVER_FDDP);
+  TrialTest r;
+  r.dV = s.cost - tr[0];
+  r.d1 = fddp ? s.dg + tr[1] : s.d1;
+  r.d2 = fddp ? s.dq - 2.0 * tr[1] : s.d2;
+  r.dVexp = alpha * (r.d1 + 0.5 * alpha * r.d2);
+  if (fddp) {
+    if (r.dVexp >= 0)
+      r.accept = (r.d1 < o.th_grad) || (r.dV > o.th_acceptstep * r.dVexp);
+    else
+      r.accept = r.dV > o.th_acceptnegstep * r.dVexp;
+  } else {
+    r.accept = (r.dVexp >= 0) && ((r.d1 < o.th_grad) || !s.is_feasible || (r.dV > o.th_acceptstep * r.dVexp));
+  }
+  return r;
+}
+
+ASLR_HD void trial_cost_finish(const SolverArgs& a, int b, int ai, double total) {
+  double* tr = a.buf.trial + ((size_t)b * ASLR_NUM_ALPHAS + ai) * 4;
+  tr[0] = total;
+  if (bad_value(total)) tr[2] = 0.0;  // crocoddyl: raiseIfNaN(cost_try) -> the trial throws
+  // Lazy line search: the costs of alpha < 1 are only needed when alpha = 1 is not taken.  tr[3] of the
+  // alpha = 1 record says "taken" (the rollout initialises it to 0 = "evaluate the other step lengths").
+  if (ai == 0 && tr[2] != 0.0 && trial_accept_test(a.buf.state[b], a.opts, 0, tr).accept) tr[3] = 1.0;
+}
+
+// whether trial (b, ai) has a trajectory whose cost is wanted
+ASLR_HD bool trial_cost_wanted(const SolverArgs& a, int b, int ai) {
+  if (a.buf.state[b].status != ASLR_OCP_RUNNING) return false;
+  if (ai > 0 && a.buf.trial[(size_t)b * ASLR_NUM_ALPHAS * 4 + 3] != 0.0) return false;  // alpha = 1 is taken
+  return a.buf.trial[((size_t)b * ASLR_NUM_ALPHAS + ai) * 4 + 2] != 0.0;
+}
+
+// serial form (host emulation): one caller sums the knots of one trial in order
+template <int N, int NU, bool VSA>
+ASLR_HD void trial_cost_body(const DevProblem<N>& P, const SolverArgs& a, int b, int ai) {
+  if (!trial_cost_wanted(a, b, ai)) return;
+  double total = 0.0;
+  for (int t = 0; t <= a.T; ++t) total += trial_knot_cost<N, NU, VSA>(P, a, b, ai, t);
+  trial_cost_finish(a, b, ai, total);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -343,21 +415,9 @@ ASLR_HD void accept_body(const SolverArgs& a, int b, int* n_done) {
     const double* tr = a.buf.trial + ((size_t)b * ASLR_NUM_ALPHAS + ai) * 4;
     if (tr[2] == 0.0) continue;  // the rollout threw (NaN / inf): try the next step length
     s.cost_try = tr[0];
-    s.dV = s.cost - tr[0];
-    if (fddp) {
-      s.d1 = s.dg + tr[1];
-      s.d2 = s.dq - 2.0 * tr[1];
-    }
-    s.dVexp = alpha * (s.d1 + 0.5 * alpha * s.d2);
-    bool acc;
-    if (fddp) {
-      if (s.dVexp >= 0)
-        acc = (s.d1 < o.th_grad) || (s.dV > o.th_acceptstep * s.dVexp);
-      else
-        acc = s.dV > o.th_acceptnegstep * s.dVexp;
-    } else {
-      acc = (s.dVexp >= 0) && ((s.d1 < o.th_grad) || !s.is_feasible || (s.dV > o.th_acceptstep * s.dVexp));
-    }
+    const TrialTest tt = trial_accept_test(s, o, ai, tr);
+    s.dV = tt.dV, s.d1 = tt.d1, s.d2 = tt.d2, s.dVexp = tt.dVexp;
+    const bool acc = tt.accept;
     if (acc) {
       s.was_feasible = s.is_feasible;
       s.is_feasible = fddp ? ((s.was_feasible || ai == 0) ? 1 : 0) : 1;

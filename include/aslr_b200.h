@@ -210,7 +210,7 @@ typedef struct AslrSolverBuffers {
   double* Quuk;    /* [B][T][nu] */
   double* xs_try;  /* [B][ASLR_NUM_ALPHAS][T+1][nx] */
   double* us_try;  /* [B][ASLR_NUM_ALPHAS][T][nu] */
-  double* trial;   /* [B][ASLR_NUM_ALPHAS][4]: cost_try, dv, ok(1/0), unused */
+  double* trial;   /* [B][ASLR_NUM_ALPHAS][4]: cost_try, dv, ok(1/0), alpha = 1 record only: step taken (1/0) */
   double* log;     /* [B][maxiter][ASLR_LOG_FIELDS], optional */
   AslrOcpState* state; /* [B] */
   int32_t* counters;   /* [4]: counters[0] = OCPs still running */

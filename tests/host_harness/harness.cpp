@@ -70,6 +70,8 @@ static int solve_t(const AslrProblemDesc* desc, const AslrBatch* batch, const As
       backward_body<GrpSerial, NX, NU>(g, sm.data(), a, b, P.u_lb, P.u_ub, P.has_limits != 0, a.buf.counters);
     for (int b = 0; b < a.B; ++b)
       for (int ai = 0; ai < ASLR_NUM_ALPHAS; ++ai) rollout_body<N, NU, VSA>(P, a, b, ai);
+    for (int b = 0; b < a.B; ++b)
+      for (int ai = 0; ai < ASLR_NUM_ALPHAS; ++ai) trial_cost_body<N, NU, VSA>(P, a, b, ai);
     for (int b = 0; b < a.B; ++b) accept_body(a, b, a.buf.counters);
     if (a.buf.counters[0] <= 0) {
       ++it;
