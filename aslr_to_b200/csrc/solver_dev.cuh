@@ -34,6 +34,32 @@ ASLR_HD void init_body(const SolverArgs& a, int b) {
   if (b == 0) a.buf.counters[0] = a.B;
 }
 
+// contiguous rows of doubles moved in 16-byte pieces when the row length is even (the row start is then 16-byte
+// aligned for every array of the solver: all row lengths involved are even as well)
+template <int LEN>
+ASLR_HD void ld_row(double* dst, const double* src) {
+  if (LEN % 2 == 0) {
+#pragma unroll
+    for (int i = 0; i < LEN; i += 2) {
+      const D2 v = *reinterpret_cast<const D2*>(src + i);
+      dst[i] = v.x, dst[i + 1 < LEN ? i + 1 : i] = v.y;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < LEN; ++i) dst[i] = src[i];
+  }
+}
+template <int LEN>
+ASLR_HD void st_row(double* dst, const double* src) {
+  if (LEN % 2 == 0) {
+#pragma unroll
+    for (int i = 0; i < LEN; i += 2) *reinterpret_cast<D2*>(dst + i) = D2{src[i], src[i + 1 < LEN ? i + 1 : i]};
+  } else {
+#pragma unroll
+    for (int i = 0; i < LEN; ++i) dst[i] = src[i];
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // K1 in solver mode: adopt the accepted trial (setCandidate), calc + calcDiff, gaps
 // (SolverDDP::calcDiff + computeDynamicFeasibility, Appendix A.2).  One thread per knot.
@@ -58,19 +84,15 @@ ASLR_HD bool calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, i
   const double* xtry = a.buf.xs_try + (((size_t)b * ASLR_NUM_ALPHAS + (slot < 0 ? 0 : slot)) * (T + 1) + t) * NX;
   if (slot >= 0) {
     const double* utry = a.buf.us_try + (((size_t)b * ASLR_NUM_ALPHAS + slot) * T + (t < T ? t : 0)) * NU;
-#pragma unroll
-    for (int i = 0; i < NX; ++i) x[i] = xtry[i], xs_b[i] = x[i];
+    ld_row<NX>(x, xtry);
+    st_row<NX>(xs_b, x);
     if (t < T) {
-#pragma unroll
-      for (int i = 0; i < NU; ++i) u[i] = utry[i], us_b[i] = u[i];
+      ld_row<NU>(u, utry);
+      st_row<NU>(us_b, u);
     }
   } else {
-#pragma unroll
-    for (int i = 0; i < NX; ++i) x[i] = xs_b[i];
-    if (t < T) {
-#pragma unroll
-      for (int i = 0; i < NU; ++i) u[i] = us_b[i];
-    }
+    ld_row<NX>(x, xs_b);
+    if (t < T) ld_row<NU>(u, us_b);
   }
   if (!running) return false;
   if (t == T) {
@@ -92,17 +114,17 @@ ASLR_HD bool calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, i
   }
   a.buf.knot_cost[(size_t)b * (T + 1) + t] = cost;
   if (t < T) {
-    double* xo = a.buf.xnext + ((size_t)b * T + t) * NX;
-#pragma unroll
-    for (int i = 0; i < NX; ++i) xo[i] = xn[i];
+    st_row<NX>(a.buf.xnext + ((size_t)b * T + t) * NX, xn);
   }
   // gaps: fs[0] = diff(xs[0], x0); fs[t+1] = diff(xs[t+1], xnext[t])
   double* fs = a.buf.fs + (size_t)b * (T + 1) * NX;
   if (!s.is_feasible) {
     if (t < T) {
-      const double* x1 = (slot >= 0) ? xtry + NX : xs_b + NX;
+      double x1[NX], gap[NX];
+      ld_row<NX>(x1, (slot >= 0) ? xtry + NX : xs_b + NX);
 #pragma unroll
-      for (int i = 0; i < NX; ++i) fs[(t + 1) * NX + i] = xn[i] - x1[i];
+      for (int i = 0; i < NX; ++i) gap[i] = xn[i] - x1[i];
+      st_row<NX>(fs + (size_t)(t + 1) * NX, gap);
     }
     if (t == 0) {
 #pragma unroll
@@ -266,27 +288,35 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
       }
     }
 #endif
-    double dx[NX];
+    // 16-byte loads / stores: each thread owns 64-byte rows 6.4 KB apart, so every 8-byte access is its own
+    // sector transaction; pairing them halves the LSU work that the dependent loads queue behind
+    double dx[NX], fsv[NX], xsv[NX], wvv[NX], Kv[NU * NX], usv[NU], kfv[NU];
+    ld_row<NX>(xsv, xs + (size_t)t * NX);
+    if (gaps) ld_row<NX>(fsv, fs + (size_t)t * NX);
+    if (need_dv) ld_row<NX>(wvv, wv + (size_t)t * NX);
+    ld_row<NU * NX>(Kv, Kg + (size_t)t * NU * NX);
+    ld_row<NU>(usv, us + (size_t)t * NU);
+    ld_row<NU>(kfv, kf + (size_t)t * NU);
 #pragma unroll
     for (int i = 0; i < NX; ++i) {
-      if (gaps) x[i] += fs[t * NX + i] * (alpha - 1.0);
-      xt[t * NX + i] = x[i];
-      dx[i] = x[i] - xs[t * NX + i];
+      if (gaps) x[i] += fsv[i] * (alpha - 1.0);
+      dx[i] = x[i] - xsv[i];
     }
+    st_row<NX>(xt + (size_t)t * NX, x);
     if (need_dv) {
 #pragma unroll
-      for (int i = 0; i < NX; ++i) dv += wv[t * NX + i] * dx[i];
+      for (int i = 0; i < NX; ++i) dv += wvv[i] * dx[i];
     }
 #pragma unroll
     for (int j = 0; j < NU; ++j) {
       double kd = 0.0;
 #pragma unroll
-      for (int i = 0; i < NX; ++i) kd += Kg[(t * NU + j) * NX + i] * dx[i];
-      double uj = us[t * NU + j] - kf[t * NU + j] * alpha - kd;
+      for (int i = 0; i < NX; ++i) kd += Kv[j * NX + i] * dx[i];
+      double uj = usv[j] - kfv[j] * alpha - kd;
       if (clamp) uj = fmin(fmax(uj, P.u_lb[j]), P.u_ub[j]);
       u[j] = uj;
-      ut[t * NU + j] = uj;
     }
+    st_row<NU>(ut + (size_t)t * NU, u);
     double c;
     KnotDeriv<N, NU> unused;
     knot_core<N, NU, VSA, false, false>(P, P.run, P.dt, x, u, Kocp, mref, xn, c, unused, nullptr, nullptr, nullptr);
@@ -331,12 +361,9 @@ ASLR_HD double trial_knot_cost(const DevProblem<N>& P, const SolverArgs& a, int 
   const double* mref = a.mref_ocp ? a.mref_ocp + (size_t)b * 12 : nullptr;
   const double* xp = a.buf.xs_try + (((size_t)b * ASLR_NUM_ALPHAS + ai) * (T + 1) + t) * NX;
   double x[NX], u[NU];
-#pragma unroll
-  for (int i = 0; i < NX; ++i) x[i] = xp[i];
+  ld_row<NX>(x, xp);
   if (t < T) {
-    const double* up = a.buf.us_try + (((size_t)b * ASLR_NUM_ALPHAS + ai) * T + t) * NU;
-#pragma unroll
-    for (int i = 0; i < NU; ++i) u[i] = up[i];
+    ld_row<NU>(u, a.buf.us_try + (((size_t)b * ASLR_NUM_ALPHAS + ai) * T + t) * NU);
   } else {
 #pragma unroll
     for (int i = 0; i < NU; ++i) u[i] = P.u_none[i];

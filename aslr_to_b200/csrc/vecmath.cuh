@@ -17,6 +17,11 @@
 
 namespace aslr {
 
+// two doubles moved as one 16-byte access
+struct alignas(16) D2 {
+  double x, y;
+};
+
 struct V3 {
   double x, y, z;
 };
