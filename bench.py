@@ -121,6 +121,25 @@ def cpu_oracle_rate(n_ocps, procs, seed=SEED):
     return iters / wall, iters, wall
 
 
+def cpu_cxx_rate(n_ocps, seed=SEED):
+    """Second CPU figure (baseline B): the very same __host__ __device__ solver source
+    compiled for the host with g++ -O2 (tests/host_harness, test infrastructure), one thread, on the first
+    `n_ocps` OCPs of the batch.  Not the reference's code path -- it shows what compiled FP64 code does."""
+    import ctypes
+    sys.path.insert(0, os.path.join(ROOT, "tests", "host_harness"))
+    import build as hb
+    import util as U
+    from aslr_to_b200 import workloads as W
+    hm = ctypes.CDLL(hb.build())
+    w = W.sea_batch(B_PER_GPU, seed=seed)
+    t0 = time.perf_counter()
+    res = U.host_solve(hm, w, ocps=list(range(n_ocps)))
+    wall = time.perf_counter() - t0
+    st = res["states"]
+    iters = int(np.sum(st["iter"] + (st["status"] == 1)))
+    return iters / wall, iters, wall
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU algorithm (oracle port: the reference's model maths on the
     NumPy restatement of crocoddyl/pinocchio -- the originals cannot be built here) on all
@@ -298,6 +317,14 @@ def run_ours(args):
             line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": 1, "kind": "port",
                                     "sample": "%d OCPs of the same batch, full FDDP solve each (%d iterations, %.1f s)"
                                               % (args.cpu_ocps, iters, wall)}
+            try:
+                crate, citers, cwall = cpu_cxx_rate(32)
+                line["cpu_cxx"] = {"value": crate, "unit": UNIT, "cores": 1,
+                                   "kind": "this repository's solver source compiled for the host (g++ -O2), not the "
+                                           "reference's code path",
+                                   "sample": "32 OCPs of the same batch (%d iterations, %.1f s)" % (citers, cwall)}
+            except Exception as e:  # no host compiler on the box: the figure is optional
+                line["cpu_cxx"] = {"unavailable": str(e)[:120]}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
