@@ -202,6 +202,20 @@ ASLR_HD bool boxqp_solve(const double* H, const double* q, const double* lb, con
 #define ASLR_PREFETCH_L2(p) ((void)0)
 #endif
 
+// where element e of a knot record (Fx | Fu | Lxx | Lxu | Luu | Lx | Lu) lives in the group's shared memory
+template <int NX, int NU>
+ASLR_HD int rec_smem_offset(int e) {
+  typedef BwdSmem<NX, NU> SM;
+  typedef Rec<NX, NU> RC;
+  if (e < RC::FU) return SM::FX + e;
+  if (e < RC::LXX) return SM::FU + (e - RC::FU);
+  if (e < RC::LXU) return SM::QXX + (e - RC::LXX);
+  if (e < RC::LUU) return SM::QXU + (e - RC::LXU);
+  if (e < RC::LX) return SM::QUU + (e - RC::LUU);
+  if (e < RC::LU) return SM::QX + (e - RC::LX);
+  return SM::QU + (e - RC::LU);
+}
+
 // One backward sweep with the current regularisation.  Returns false on "backward_error".
 template <class Grp, int NX, int NU>
 ASLR_HD bool backward_sweep(const Grp& g, double* sm, const SolverArgs& a, int b, const double* u_lb,
@@ -250,16 +264,38 @@ ASLR_HD bool backward_sweep(const Grp& g, double* sm, const SolverArgs& a, int b
     }
   }
 
+  // small models: each lane keeps its slice of the NEXT knot record in registers (one knot of lead time)
+  constexpr bool PIPE = (NX * NX < 256) && (G > 1);
+  constexpr int NSL = PIPE ? (RC::SIZE + G - 1) / G : 1;
+  double nxt[NSL];
+  if (PIPE) {
+#pragma unroll
+    for (int m = 0; m < NSL; ++m) {
+      const int e = g.lane + m * G;
+      nxt[m] = (e < RC::SIZE) ? deriv[(size_t)(T - 1) * RC::SIZE + e] : 0.0;
+    }
+  }
   for (int t = T - 1; t >= 0; --t) {
     const double* rec = deriv + (size_t)t * RC::SIZE;
-    // ---- load the knot record (prefetched into L1 one knot ahead, into L2 two knots ahead)
-    if (t >= 1) ASLR_GFOR(e, LINES) ASLR_PREFETCH_L1(rec - RC::SIZE + e * 16);
-    if (t >= 2) ASLR_GFOR(e, LINES) ASLR_PREFETCH_L2(rec - 2 * RC::SIZE + e * 16);
-    ASLR_GFOR(e, NX * NX) sm[SM::FX + e] = rec[RC::FX + e], sm[SM::QXX + e] = rec[RC::LXX + e];
-    ASLR_GFOR(e, NX * NU) sm[SM::FU + e] = rec[RC::FU + e], sm[SM::QXU + e] = rec[RC::LXU + e];
-    ASLR_GFOR(e, NU * NU) sm[SM::QUU + e] = rec[RC::LUU + e];
-    ASLR_GFOR(e, NX) sm[SM::QX + e] = rec[RC::LX + e], sm[SM::FS + e] = feasible ? 0.0 : fs[t * NX + e];
-    ASLR_GFOR(e, NU) sm[SM::QU + e] = rec[RC::LU + e];
+    if (PIPE) {
+      // ---- the record was fetched into registers during the previous knot (see below): scatter it
+#pragma unroll
+      for (int m = 0; m < NSL; ++m) {
+        const int e = g.lane + m * G;
+        if (e < RC::SIZE) sm[rec_smem_offset<NX, NU>(e)] = nxt[m];
+      }
+      ASLR_GFOR(e, NX) sm[SM::FS + e] = feasible ? 0.0 : fs[t * NX + e];
+      if (t >= 2) ASLR_GFOR(e, LINES) ASLR_PREFETCH_L2(rec - 2 * RC::SIZE + e * 16);
+    } else {
+      // ---- load the knot record (prefetched into L1 one knot ahead, into L2 two knots ahead)
+      if (t >= 1) ASLR_GFOR(e, LINES) ASLR_PREFETCH_L1(rec - RC::SIZE + e * 16);
+      if (t >= 2) ASLR_GFOR(e, LINES) ASLR_PREFETCH_L2(rec - 2 * RC::SIZE + e * 16);
+      ASLR_GFOR(e, NX * NX) sm[SM::FX + e] = rec[RC::FX + e], sm[SM::QXX + e] = rec[RC::LXX + e];
+      ASLR_GFOR(e, NX * NU) sm[SM::FU + e] = rec[RC::FU + e], sm[SM::QXU + e] = rec[RC::LXU + e];
+      ASLR_GFOR(e, NU * NU) sm[SM::QUU + e] = rec[RC::LUU + e];
+      ASLR_GFOR(e, NX) sm[SM::QX + e] = rec[RC::LX + e], sm[SM::FS + e] = feasible ? 0.0 : fs[t * NX + e];
+      ASLR_GFOR(e, NU) sm[SM::QU + e] = rec[RC::LU + e];
+    }
     g.sync();
     // ---- A = Fx^T Vxx', FuV = Fu^T Vxx', Qx += Fx^T Vx', Qu += Fu^T Vx'
     ASLR_GFOR(e, NX * NX) {
@@ -310,6 +346,15 @@ ASLR_HD bool backward_sweep(const Grp& g, double* sm, const SolverArgs& a, int b
 #pragma unroll
       for (int k = 0; k < NX; ++k) s += sm[SM::FUV + i * NX + k] * sm[SM::FU + k * NU + j];
       sm[SM::QUU + e] += s + ((i == j) ? xreg : 0.0);
+    }
+    if (PIPE && t >= 1) {
+      // the record of knot t - 1 starts its trip now and lands in registers while the gains, the value
+      // update and the stores of this knot run; nothing of this knot depends on it
+#pragma unroll
+      for (int m = 0; m < NSL; ++m) {
+        const int e = g.lane + m * G;
+        nxt[m] = (e < RC::SIZE) ? rec[e - RC::SIZE] : 0.0;
+      }
     }
     g.sync();
     // ---- computeGains
