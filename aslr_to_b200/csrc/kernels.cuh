@@ -15,6 +15,8 @@
 #endif
 #ifndef ASLR_BWD_CTA_THREADS
 #define ASLR_BWD_CTA_THREADS 128  // nx = 28 backward pass: threads per OCP and minimum resident CTAs per SM
+#endif
+#ifndef ASLR_BWD_CTA_MINB
 #define ASLR_BWD_CTA_MINB 4
 #endif
 #ifndef ASLR_BWD_GS

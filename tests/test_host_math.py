@@ -84,3 +84,21 @@ def test_batch_members_match_golden_trace(hostmath, solver):
     res = host_solve(hostmath, w, ocps=[0, 1])
     for b in (0, 1):
         compare_solver_trace(res, b, golden("solve_sea_batch_%s_b%d" % (solver, b)))
+
+
+def test_chain7_solver_host_build_matches_oracle_port(hostmath):
+    """nx = 28 path of the backward pass (register-tiled products) and the 7-DOF rollout, serial host build
+    against the oracle solver: 2 OCPs, T = 6, 3 iterations."""
+    import oracle_build as ob
+    from util import host_solve, rel_err
+    w = W.chain7_batch(B=2, T=6)
+    w["maxiter"] = 3
+    res = host_solve(hostmath, w)
+    for b in (0, 1):
+        solver, log = ob.solve(w, b, "port")
+        it = len(log.costs)
+        assert rel_err(res["log"][b][:it, 0], log.costs) < 1e-9
+        assert rel_err(res["log"][b][:it, 3], log.steps) == 0
+        assert rel_err(res["xs"][b], np.array(solver.xs)) < 1e-9
+        assert rel_err(res["Kgain"][b], np.array(solver.K)) < 1e-8
+        assert rel_err(res["Vxx"][b], np.array(solver.Vxx)) < 1e-9
