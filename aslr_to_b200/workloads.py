@@ -133,6 +133,16 @@ def chain7_batch(B=1024, T=200, seed=20240002):
                 solver="fddp", th_stop=1e-7, maxiter=100, init="x0-zero-u", u_lb=None, u_ub=None)
 
 
+def chain7_vsa_batch(B=2, T=20, seed=20240003):
+    """7-link variable-stiffness arm under SolverBoxDDP (nx = 28, nu = 14): the 7-DOF counterpart of
+    examples/two_dof_vsa_boxddp.py, with the stiffness bound starting active (sigma_lb > initial guess)."""
+    w = chain7_batch(B, T, seed)
+    running = _sorted([t for t in w["running"] if t["kind"] != "control"] +
+                      [_term("uReg", "control", 1e-2, np.zeros(14), np.ones(14))])
+    return dict(w, name="chain7_vsa_batch_%d" % B, kind="vsa", K=None, running=running, solver="boxddp",
+                u_lb=np.array([-50.0] * 7 + [5.0] * 7), u_ub=np.array([50.0] * 7 + [100.0] * 7))
+
+
 # ------------------------------------------------------------------------------------------------
 _KIND = {"placement": A.COST_FRAME_PLACEMENT, "state": A.COST_STATE, "control": A.COST_CONTROL,
          "stiffness": A.COST_STIFFNESS, "pendulum": A.COST_DOUBLE_PENDULUM}

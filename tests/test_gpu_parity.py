@@ -131,9 +131,11 @@ def test_oracle_port_on_seeded_batch_members(BT):
         assert rel_err(res["kff"][b], np.array(solver.k)) < RTOL
 
 
-def test_chain7_solve_matches_oracle_port(BT):
-    """nx = 28 path (CTA-per-OCP backward pass): 2 OCPs, T = 12, 4 iterations."""
-    w = W.chain7_batch(B=2, T=12)
+@pytest.mark.parametrize("kind", ["sea", "vsa"])
+def test_chain7_solve_matches_oracle_port(BT, kind):
+    """nx = 28 path (CTA-per-OCP backward pass): 2 OCPs, T = 12, 4 iterations; FDDP on the SEA arm
+    (nu = 7) and BoxDDP with active stiffness bounds on the VSA arm (nu = 14)."""
+    w = W.chain7_batch(B=2, T=12) if kind == "sea" else W.chain7_vsa_batch(B=2, T=12)
     w["maxiter"] = 4
     res = gpu_solve(BT, w)
     for b in (0, 1):

@@ -86,12 +86,13 @@ def test_batch_members_match_golden_trace(hostmath, solver):
         compare_solver_trace(res, b, golden("solve_sea_batch_%s_b%d" % (solver, b)))
 
 
-def test_chain7_solver_host_build_matches_oracle_port(hostmath):
-    """nx = 28 path of the backward pass (register-tiled products) and the 7-DOF rollout, serial host build
-    against the oracle solver: 2 OCPs, T = 6, 3 iterations."""
+@pytest.mark.parametrize("kind", ["sea", "vsa"])
+def test_chain7_solver_host_build_matches_oracle_port(hostmath, kind):
+    """nx = 28 path of the backward pass and the 7-DOF rollout, serial host build against the oracle solver:
+    2 OCPs, T = 6, 3 iterations; FDDP on the SEA arm (nu = 7), BoxDDP on the VSA arm (nu = 14)."""
     import oracle_build as ob
     from util import host_solve, rel_err
-    w = W.chain7_batch(B=2, T=6)
+    w = W.chain7_batch(B=2, T=6) if kind == "sea" else W.chain7_vsa_batch(B=2, T=6)
     w["maxiter"] = 3
     res = host_solve(hostmath, w)
     for b in (0, 1):
