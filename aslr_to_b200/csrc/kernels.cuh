@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 
 #include "backward_dev.cuh"
+#include "rollout_coop.cuh"
 
 #ifndef ASLR_ROLL_THREADS
 #define ASLR_ROLL_THREADS 64  // 2-DOF rollout: CTA size and minimum resident CTAs per SM (one wave for 40960 trials)
@@ -18,6 +19,18 @@
 #endif
 #ifndef ASLR_BWD_CTA_MINB
 #define ASLR_BWD_CTA_MINB 4
+#endif
+#ifndef ASLR_K1_STAGE_MAXN
+#define ASLR_K1_STAGE_MAXN 7  // largest link DOF whose K1 stages its record stores through shared memory
+#endif
+#ifndef ASLR_ROLLC_GS
+// n > 2 rollout: lanes per trial, trials per CTA, minimum resident CTAs per SM.  12 trials of 2.8 KB + the
+// model constants = 37.6 KB per CTA: 6 CTAs = 72 trials per SM, so the 10 240 trials of 1024 OCPs are one wave
+// (measured: 3.59 ms against 4.49 ms for 16 trials x 3 CTAs, 4.95 ms for 4 lanes per trial)
+#define ASLR_ROLLC_GS 8
+#define ASLR_ROLLC_TRIALS 12
+#define ASLR_ROLLC_MINB 6
+#define ASLR_ROLLC_MINN 3     // smallest link DOF that uses the lane-cooperative rollout
 #endif
 #ifndef ASLR_BWD_GS
 #define ASLR_BWD_GS 16  // lanes per OCP in the nx = 8 backward pass
@@ -95,7 +108,7 @@ template <int N, int NU, bool VSA, bool DIFF>
 __global__ void __launch_bounds__(128, (N <= 2) ? ASLR_K1_MINB : 1) knot_kernel(const __grid_constant__ DevProblem<N> P, const KnotArgs a) {
   constexpr int NX = 4 * N;
   typedef Rec<NX, NU> RC;
-  constexpr bool STAGED = DIFF && (N <= 2);
+  constexpr bool STAGED = DIFF && (N <= ASLR_K1_STAGE_MAXN);
   extern __shared__ double stage[];
   const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
   const long total = (long)a.B * (a.T + 1);
@@ -152,7 +165,7 @@ __global__ void __launch_bounds__(128, (N <= 2) ? ASLR_K1_MINB : 1) solver_calcd
   extern __shared__ double stage[];
   const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
   const long total = (long)a.B * (a.T + 1);
-  if constexpr (N <= 2) {
+  if constexpr (N <= ASLR_K1_STAGE_MAXN) {
     const bool live = g < total;
     const long gc = live ? g : total - 1;
     KnotDeriv<N, NU> kd;
@@ -174,6 +187,23 @@ __global__ void __launch_bounds__((N <= 2) ? ASLR_ROLL_THREADS : 64, (N <= 2) ? 
   const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= (long)a.B * ASLR_NUM_ALPHAS) return;
   rollout_body<N, NU, VSA>(P, a, (int)(g / ASLR_NUM_ALPHAS), (int)(g % ASLR_NUM_ALPHAS));
+}
+
+// K3 for the larger models: GS lanes per trial, per-knot state in shared memory (rollout_coop.cuh)
+template <int N, int NU, bool VSA, int GS, int TRIALS>
+__global__ void __launch_bounds__(GS * TRIALS, ASLR_ROLLC_MINB) rollout_coop_kernel(const __grid_constant__ DevProblem<N> P,
+                                                                                    const SolverArgs a) {
+  extern __shared__ double smem[];
+  for (int i = threadIdx.x; i < N; i += blockDim.x) model_const_fill<N>(P, smem, i);
+  __syncthreads();
+  const int w = threadIdx.x / GS;
+  const long trial = (long)blockIdx.x * TRIALS + w;
+  if (trial >= (long)a.B * ASLR_NUM_ALPHAS) return;
+  const int lane = threadIdx.x % GS;
+  const unsigned mask = (GS == 32) ? 0xffffffffu : (((1u << GS) - 1u) << ((threadIdx.x & 31) - lane));
+  GrpSub<GS> g{lane, mask};
+  rollout_coop_body<GrpSub<GS>, N, NU, VSA>(g, smem + ModelConst<N>::SIZE + (size_t)w * RollSmem<N, NU>::SIZE, smem, P, a,
+                                            (int)(trial / ASLR_NUM_ALPHAS), (int)(trial % ASLR_NUM_ALPHAS));
 }
 
 // K3b: one warp per trial; lanes take the knots 32 at a time, the costs are then added in knot order
@@ -259,7 +289,7 @@ struct Launch {
 
   // shared-memory staging of the coalesced record stores (2-DOF kernels only)
   static size_t stage_bytes(int threads) {
-    return (N <= 2) ? sizeof(double) * RecParts<Rec<NX, NU>::SIZE>::WARP_DOUBLES * (threads / 32) : 0;
+    return (N <= ASLR_K1_STAGE_MAXN) ? sizeof(double) * RecParts<Rec<NX, NU>::SIZE>::WARP_DOUBLES * (threads / 32) : 0;
   }
   static int knots(const void* Pv, const KnotArgs& a, int diff, cudaStream_t s) {
     const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
@@ -268,7 +298,7 @@ struct Launch {
     const int threads = 128;
     const unsigned blocks = (unsigned)((total + threads - 1) / threads);
     if (diff) {
-      if (N <= 2)
+      if (N <= ASLR_K1_STAGE_MAXN)
         cudaFuncSetAttribute(knot_kernel<N, NU, VSA, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)stage_bytes(threads));
       knot_kernel<N, NU, VSA, true><<<blocks, threads, stage_bytes(threads), s>>>(P, a);
@@ -281,7 +311,7 @@ struct Launch {
     const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
     const long total = (long)a.B * (a.T + 1);
     const int threads = 128;
-    if (N <= 2)
+    if (N <= ASLR_K1_STAGE_MAXN)
       cudaFuncSetAttribute(solver_calcdiff_kernel<N, NU, VSA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)stage_bytes(threads));
     solver_calcdiff_kernel<N, NU, VSA>
@@ -291,8 +321,16 @@ struct Launch {
   static int rollout(const void* Pv, const SolverArgs& a, cudaStream_t s) {
     const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
     const long total = (long)a.B * ASLR_NUM_ALPHAS;
-    const int threads = (N <= 2) ? ASLR_ROLL_THREADS : 64;
-    rollout_kernel<N, NU, VSA><<<(unsigned)((total + threads - 1) / threads), threads, 0, s>>>(P, a);
+    if constexpr (N >= ASLR_ROLLC_MINN) {
+      constexpr int GS = ASLR_ROLLC_GS, TRIALS = ASLR_ROLLC_TRIALS;
+      constexpr size_t bytes = sizeof(double) * (ModelConst<N>::SIZE + (size_t)TRIALS * RollSmem<N, NU>::SIZE);
+      auto k = rollout_coop_kernel<N, NU, VSA, GS, TRIALS>;
+      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+      k<<<(unsigned)((total + TRIALS - 1) / TRIALS), GS * TRIALS, bytes, s>>>(P, a);
+    } else {
+      const int threads = ASLR_ROLL_THREADS;
+      rollout_kernel<N, NU, VSA><<<(unsigned)((total + threads - 1) / threads), threads, 0, s>>>(P, a);
+    }
     if (launch_status()) return -2;
     trial_cost_kernel<N, NU, VSA><<<(unsigned)(((long)a.B * 32 + 127) / 128), 128, 0, s>>>(P, a, 0);
     trial_cost_kernel<N, NU, VSA>

@@ -37,10 +37,10 @@ K1_DRAM_TRAFFIC_PER_LAUNCH = 773.4e6  # dram__bytes_read + write of one knot_ker
 ALGO_BYTES_PER_KNOT = 1544  # 2-DOF SEA, read x,u; write xnext,cost,Fx,Fu,Lx,Lu,Lxx,Lxu,Luu
 
 
-def workload_config(n_gpus):
-    return {"workload": "4096 x 2-DOF SEA FDDP reaching OCPs per GPU (BASELINE.json configs[3]), T=100, "
-                        "th_stop=1e-7, maxiter=100, solved to convergence",
-            "ocps_per_gpu": B_PER_GPU, "T": 100, "nx": 8, "nu": 2, "solver": "fddp",
+def workload_config(n_gpus, solver="fddp"):
+    return {"workload": "4096 x 2-DOF SEA %s reaching OCPs per GPU (BASELINE.json configs[3]), T=100, "
+                        "th_stop=1e-7, maxiter=100, solved to convergence" % solver.upper(),
+            "ocps_per_gpu": B_PER_GPU, "T": 100, "nx": 8, "nu": 2, "solver": solver,
             "parallelism": "independent OCPs sharded over %d GPU(s), no per-iteration collective" % n_gpus,
             "l2": "per-iteration working set (derivative records 576 MB + trial trajectories 331 MB per GPU) "
                   "exceeds the 126 MB L2, no explicit flush"}
@@ -121,22 +121,38 @@ def cpu_oracle_rate(n_ocps, procs, seed=SEED):
     return iters / wall, iters, wall
 
 
-def cpu_cxx_rate(n_ocps, seed=SEED):
-    """Second CPU figure (SURVEY.md section 8d, baseline B): the very same __host__ __device__ solver source
-    compiled for the host with g++ -O2 (tests/host_harness, test infrastructure), one thread, on the first
-    `n_ocps` OCPs of the batch.  Not the reference's code path -- it shows what compiled FP64 code does."""
+def _cxx_worker(args):
+    lo, hi, seed = args
     import ctypes
     sys.path.insert(0, os.path.join(ROOT, "tests", "host_harness"))
     import build as hb
     import util as U
     from aslr_to_b200 import workloads as W
-    hm = ctypes.CDLL(hb.build())
+    hm = ctypes.CDLL(hb.LIB)
     w = W.sea_batch(B_PER_GPU, seed=seed)
     t0 = time.perf_counter()
-    res = U.host_solve(hm, w, ocps=list(range(n_ocps)))
-    wall = time.perf_counter() - t0
+    res = U.host_solve(hm, w, ocps=list(range(lo, hi)))
     st = res["states"]
-    iters = int(np.sum(st["iter"] + (st["status"] == 1)))
+    return int(np.sum(st["iter"] + (st["status"] == 1))), time.perf_counter() - t0
+
+
+def cpu_cxx_rate(n_ocps, procs=1, seed=SEED):
+    """Second CPU figure (SURVEY.md section 8d, baseline B): the very same __host__ __device__ solver source
+    compiled for the host with g++ -O2 (tests/host_harness, test infrastructure) on `n_ocps` OCPs of the batch
+    per process, `procs` processes over disjoint OCP ranges.  Not the reference's code path -- it shows what
+    compiled FP64 code does on the host cores.  Returns (rate over the workers' own solve time, iterations,
+    slowest worker's solve time)."""
+    import multiprocessing as mp
+    sys.path.insert(0, os.path.join(ROOT, "tests", "host_harness"))
+    import build as hb
+    hb.build()
+    jobs = [(i * n_ocps, (i + 1) * n_ocps, seed) for i in range(procs)]
+    if procs == 1:
+        res = [_cxx_worker(jobs[0])]
+    else:
+        with mp.get_context("spawn").Pool(procs) as pool:
+            res = pool.map(_cxx_worker, jobs)
+    iters, wall = sum(r[0] for r in res), max(r[1] for r in res)
     return iters / wall, iters, wall
 
 
@@ -184,10 +200,10 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    w = W.sea_batch(B_PER_GPU, seed=SEED + rank)
+    w = W.sea_batch(B_PER_GPU, seed=SEED + rank, solver=args.solver)
     B, T, nx, nu = B_PER_GPU, w["T"], 8, 2
     prob = BT.BatchedShootingProblem(W.to_desc(w), w["x0"], T, K_ocp=w["K_ocp"], device=dev)
-    solver = BT.BatchedSolver(prob, A.SOLVER_FDDP, maxiter=w["maxiter"], th_stop=w["th_stop"], store_vxx=False,
+    solver = BT.BatchedSolver(prob, W.SOLVER_KIND[args.solver], maxiter=w["maxiter"], th_stop=w["th_stop"], store_vxx=False,
                               store_quu=False, store_log=False)
     xs0_h, us0_h = initial_guess_arrays(w, np.asarray(w["x0"]), T, nu)
     # pinned host buffers = what a caller of the public API holds
@@ -244,6 +260,21 @@ def run_ours(args):
         torch.cuda.synchronize()
         print(json.dumps({"profile": True, "kernel_launches_per_solve": int(solver.result.kernel_launches)}))
         return
+    if args.profile_floor:  # for ncu: the latency floor = a batch holding only the OCPs that never converge
+        step_device()
+        torch.cuda.synchronize()
+        idx = np.nonzero(solver.states()["status"] != A.OCP_CONVERGED)[0]
+        x0f, Kf = np.asarray(w["x0"])[idx], np.asarray(w["K_ocp"])[idx]
+        probf = BT.BatchedShootingProblem(W.to_desc(w), x0f, T, K_ocp=Kf, device=dev)
+        solf = BT.BatchedSolver(probf, W.SOLVER_KIND[args.solver], maxiter=w["maxiter"], th_stop=w["th_stop"],
+                                store_vxx=False, store_quu=False, store_log=False)
+        xf, uf = initial_guess_arrays(w, x0f, T, nu)
+        for _ in range(2):
+            solf.solve(xf, uf)
+            torch.cuda.synchronize()
+        print(json.dumps({"profile_floor": True, "ocps": idx.tolist(),
+                          "iters": solf.states()["iter"].tolist()}))
+        return
     for _ in range(max(args.warmup, 3)):
         step_device()
     torch.cuda.synchronize()
@@ -291,12 +322,24 @@ def run_ours(args):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = ALGO_BYTES_PER_KNOT * knots / (ms_k1 * 1e-3) / 1e9
 
+    # ---- where one solve spends its time: CUDA events around every stage of one more solve (untimed extra)
+    rows = np.array(stage_event_times(prob, solver, w, w["maxiter"], W.SOLVER_KIND[args.solver]))
+    stage_ms = rows.sum(0) * 1e-3
+    stages = {"ms_per_solve": dict(zip(STAGES, [round(float(v), 3) for v in stage_ms])),
+              "share": dict(zip(STAGES, [round(float(v / stage_ms.sum()), 3) for v in stage_ms])),
+              "full_batch_us": dict(zip(STAGES, [float(v) for v in rows[1]])),
+              "floor_us": dict(zip(STAGES, [float(v) for v in rows[-1]])),
+              "fp64_pipe_frac_ncu": {"calcdiff": 0.25, "backward": 0.20, "rollout": 0.41},
+              "note": "stepwise ABI with one event pair and one sync per stage, after the timed region; full_batch = "
+                      "iteration 1, floor = last iteration (stragglers only); FP64-pipe utilisation of each kernel at "
+                      "full batch from profiles/r01c_ncu_full.md (measured FP64 peak 34.2 TFLOP/s)"}
+
     if rank == 0:
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "metric": METRIC.replace("fddp", args.solver), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(world),
+            "config": workload_config(world, args.solver),
             "ocp_iters_per_solve_all_gpus": total_iters, "converged_rank0": n_conv,
             "calcdiff_knots_per_s": knots_per_s, "calcdiff_ms": ms_k1,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
@@ -310,7 +353,7 @@ def run_ours(args):
                          "traffic_source": "ncu --set full capture of this kernel, profiles/r01b_ncu_full.md",
                          "fp64": {"dfma_latency_cycles": 8.2, "peak_tflops_measured": 34.2,
                                   "source": "tools/fp64_peak.cu on this pool, profiles/r01b_fp64_peak.json"}},
-            "clocks": clocks,
+            "clocks": clocks, "stages": stages,
         }
         if world == 1 and not args.no_cpu:
             rate, iters, wall = cpu_oracle_rate(args.cpu_ocps, 1)
@@ -318,11 +361,17 @@ def run_ours(args):
                                     "sample": "%d OCPs of the same batch, full FDDP solve each (%d iterations, %.1f s)"
                                               % (args.cpu_ocps, iters, wall)}
             try:
+                kind = "this repository's solver source compiled for the host (g++ -O2), not the reference's code path"
                 crate, citers, cwall = cpu_cxx_rate(32)
-                line["cpu_cxx"] = {"value": crate, "unit": UNIT, "cores": 1,
-                                   "kind": "this repository's solver source compiled for the host (g++ -O2), not the "
-                                           "reference's code path",
+                line["cpu_cxx"] = {"value": crate, "unit": UNIT, "cores": 1, "kind": kind,
                                    "sample": "32 OCPs of the same batch (%d iterations, %.1f s)" % (citers, cwall)}
+                cores = os.cpu_count() or 1
+                if cores > 1:
+                    crate, citers, cwall = cpu_cxx_rate(32, cores)
+                    line["cpu_cxx_all_cores"] = {
+                        "value": crate, "unit": UNIT, "cores": cores, "kind": kind,
+                        "sample": "32 OCPs per core, %d processes (%d iterations, slowest worker %.1f s)"
+                                  % (cores, citers, cwall)}
             except Exception as e:  # no host compiler on the box: the figure is optional
                 line["cpu_cxx"] = {"unavailable": str(e)[:120]}
         print(json.dumps(line))
@@ -380,9 +429,37 @@ def run_chain7_mpc(args):
         "gpu_launches": int(mpc.solver.result.kernel_launches) * args.steps}))
 
 
+STAGES = ("calcdiff", "backward", "rollout", "accept")
+
+
+def stage_event_times(prob, solver, w, n_iters, kind):
+    """CUDA-event time (us) of the four stages of the first `n_iters` solver iterations, driven through the
+    stepwise ABI from the workload's initial guess: rows of [calcdiff, backward, rollout + trial costs, accept]."""
+    import ctypes as C
+    import torch
+    from aslr_to_b200 import _abi as A, batched as BT, workloads as W
+    xs0, us0 = W.initial_guess(w, np.asarray(w["x0"]), prob.T, prob.nu)
+    solver.set_candidate(xs0, us0)
+    lib, bs, st = prob.lib, prob.batch_struct(), prob._stream()
+    opts = BT.make_opts(kind, w["maxiter"], w["th_stop"], lib=lib)
+    A.check(lib.aslr_solver_init(prob.handle, C.byref(bs), C.byref(opts), C.byref(solver.buf), st))
+    rows = []
+    for it in range(n_iters):
+        row = []
+        for fn, extra in ((lib.aslr_solver_calc_diff, (it,)), (lib.aslr_backward_pass, ()),
+                          (lib.aslr_forward_pass, ()), (lib.aslr_accept_step, (it,))):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            A.check(fn(prob.handle, C.byref(bs), C.byref(opts), C.byref(solver.buf), *extra, st))
+            e1.record()
+            torch.cuda.synchronize()
+            row.append(round(e0.elapsed_time(e1) * 1e3, 1))
+        rows.append(row)
+    return rows
+
+
 def run_kernel_times(args):
     """--kernels N: CUDA-event time of each solver kernel in the first N iterations (full batch active)."""
-    import ctypes as C
     import torch
     from aslr_to_b200 import _abi as A, batched as BT, workloads as W
     torch.cuda.set_device(0)
@@ -394,23 +471,7 @@ def run_kernel_times(args):
         prob = BT.BatchedShootingProblem(W.to_desc(w), w["x0"], w["T"], K_ocp=w["K_ocp"])
     solver = BT.BatchedSolver(prob, A.SOLVER_FDDP, maxiter=w["maxiter"], th_stop=w["th_stop"], store_vxx=False,
                               store_quu=False, store_log=False)
-    xs0, us0 = W.initial_guess(w, np.asarray(w["x0"]), prob.T, prob.nu)
-    solver.set_candidate(xs0, us0)
-    lib, bs, st = prob.lib, prob.batch_struct(), prob._stream()
-    opts = BT.make_opts(A.SOLVER_FDDP, w["maxiter"], w["th_stop"], lib=lib)
-    A.check(lib.aslr_solver_init(prob.handle, C.byref(bs), C.byref(opts), C.byref(solver.buf), st))
-    rows = []
-    for it in range(args.kernels):
-        row = []
-        for fn, extra in ((lib.aslr_solver_calc_diff, (it,)), (lib.aslr_backward_pass, ()),
-                          (lib.aslr_forward_pass, ()), (lib.aslr_accept_step, (it,))):
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            A.check(fn(prob.handle, C.byref(bs), C.byref(opts), C.byref(solver.buf), *extra, st))
-            e1.record()
-            torch.cuda.synchronize()
-            row.append(round(e0.elapsed_time(e1) * 1e3, 1))
-        rows.append(row)
+    rows = stage_event_times(prob, solver, w, args.kernels, A.SOLVER_FDDP)
     print(json.dumps({"workload": args.workload, "kernel_us_per_iteration[calcdiff,backward,rollout,accept]": rows}))
 
 
@@ -424,8 +485,11 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--kernels", type=int, default=0, help="time each kernel of the first N iterations")
     ap.add_argument("--profile", action="store_true", help="two solves only (for ncu launch lists)")
+    ap.add_argument("--profile-floor", action="store_true",
+                    help="one full solve, then two solves of only the never-converging OCPs (for ncu: the latency floor)")
     ap.add_argument("--workload", default="sea4096", choices=["sea4096", "chain7_mpc"])
     ap.add_argument("--chain7-ocps", type=int, default=1024)
+    ap.add_argument("--solver", default="fddp", choices=["fddp", "ddp"], help="sea4096 workload: SolverFDDP (headline) or SolverDDP")
     args = ap.parse_args()
     if args.kernels:
         run_kernel_times(args)

@@ -46,6 +46,7 @@ extern "C" int hh_knot_eval(const AslrProblemDesc* desc, int terminal, int diff,
 #include <vector>
 
 #include "backward_dev.cuh"
+#include "rollout_coop.cuh"
 
 template <int N, bool VSA>
 static int solve_t(const AslrProblemDesc* desc, const AslrBatch* batch, const AslrSolverOpts* opts,
@@ -58,7 +59,7 @@ static int solve_t(const AslrProblemDesc* desc, const AslrBatch* batch, const As
   a.x0 = batch->x0, a.K_ocp = batch->K_ocp, a.mref_ocp = batch->mref_ocp;
   a.buf = *buf;
   a.opts = *opts;
-  std::vector<double> sm(BwdSmem<NX, NU>::SIZE);
+  std::vector<double> sm(BwdSmem<NX, NU>::SIZE), rs(RollSmem<N, NU>::SIZE), mc(ModelConst<N>::SIZE);
   for (int b = 0; b < a.B; ++b) init_body(a, b);
   int it = 0;
   for (it = 0; it < opts->maxiter; ++it) {
@@ -69,7 +70,14 @@ static int solve_t(const AslrProblemDesc* desc, const AslrBatch* batch, const As
     for (int b = 0; b < a.B; ++b)
       backward_body<GrpSerial, NX, NU>(g, sm.data(), a, b, P.u_lb, P.u_ub, P.has_limits != 0, a.buf.counters);
     for (int b = 0; b < a.B; ++b)
-      for (int ai = 0; ai < ASLR_NUM_ALPHAS; ++ai) rollout_body<N, NU, VSA>(P, a, b, ai);
+      for (int ai = 0; ai < ASLR_NUM_ALPHAS; ++ai) {
+        if (N >= 3) {  // same split as the CUDA launcher: lane-cooperative form (one serial "lane" here) for n > 2
+          for (int i = 0; i < N; ++i) model_const_fill<N>(P, mc.data(), i);
+          rollout_coop_body<GrpSerial, N, NU, VSA>(g, rs.data(), mc.data(), P, a, b, ai);
+        } else {
+          rollout_body<N, NU, VSA>(P, a, b, ai);
+        }
+      }
     for (int b = 0; b < a.B; ++b)
       for (int ai = 0; ai < ASLR_NUM_ALPHAS; ++ai) trial_cost_body<N, NU, VSA>(P, a, b, ai);
     for (int b = 0; b < a.B; ++b) accept_body(a, b, a.buf.counters);
