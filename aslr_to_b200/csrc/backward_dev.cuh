@@ -12,12 +12,14 @@ namespace aslr {
 // thread-group policies -----------------------------------------------------------------------
 struct GrpSerial {  // host emulation: one thread plays the whole group
   static constexpr int G = 1;
+  static constexpr bool COLS = false;
   int lane;
   ASLR_HD void sync() const {}
 };
 #if defined(__CUDACC__)
 struct GrpWarp {
   static constexpr int G = 32;
+  static constexpr bool COLS = false;
   int lane;
   __device__ __forceinline__ void sync() const { __syncwarp(); }
 };
@@ -25,6 +27,7 @@ struct GrpWarp {
 template <int GS>
 struct GrpSub {
   static constexpr int G = GS;
+  static constexpr bool COLS = false;
   int lane;
   unsigned mask;
   __device__ __forceinline__ void sync() const { __syncwarp(mask); }
@@ -32,6 +35,7 @@ struct GrpSub {
 template <int THREADS>
 struct GrpCta {
   static constexpr int G = THREADS;
+  static constexpr bool COLS = false;
   int lane;
   __device__ __forceinline__ void sync() const { __syncthreads(); }
 };
@@ -634,6 +638,12 @@ ASLR_HD bool backward_sweep(const Grp& g, double* sm, const SolverArgs& a, int b
   return true;
 }
 
+}  // namespace aslr
+#if defined(__CUDACC__)
+#include "backward_cols.cuh"  // row-per-lane sweep for small models (device only)
+#endif
+namespace aslr {
+
 // computeDirection() (minus calcDiff, done by K1) + expected-improvement terms for one OCP
 template <class Grp, int NX, int NU>
 ASLR_HD void backward_body(const Grp& g, double* sm, const SolverArgs& a, int b, const double* u_lb,
@@ -663,7 +673,13 @@ ASLR_HD void backward_body(const Grp& g, double* sm, const SolverArgs& a, int b,
   double sums[6];
   int retries = 0;
   while (true) {
-    const bool ok = backward_sweep<Grp, NX, NU>(g, sm, a, b, u_lb, u_ub, box_limits, xreg, sums);
+    bool ok;
+#if defined(__CUDACC__)
+    if constexpr (Grp::COLS)
+      ok = backward_sweep_cols<NX, NU>(g, sm, a, b, u_lb, u_ub, box_limits, xreg, sums);
+    else
+#endif
+      ok = backward_sweep<Grp, NX, NU>(g, sm, a, b, u_lb, u_ub, box_limits, xreg, sums);
     g.sync();
     if (ok) break;
     // catch (backward_error): recalcDiff = false; increaseRegularization(); give up at reg_max

@@ -32,6 +32,10 @@
 #define ASLR_ROLLC_MINB 6
 #define ASLR_ROLLC_MINN 3     // smallest link DOF that uses the lane-cooperative rollout
 #endif
+#ifndef ASLR_BWD_COLS
+#define ASLR_BWD_COLS 1         // nx = 8 backward pass: row-per-lane sweep (backward_cols.cuh), 8 lanes per OCP
+#define ASLR_BWD_COLS_GROUPS 4  // OCPs per CTA (one warp)
+#endif
 #ifndef ASLR_BWD_GS
 #define ASLR_BWD_GS 16  // lanes per OCP in the nx = 8 backward pass
 #endif
@@ -262,6 +266,20 @@ __global__ void __launch_bounds__(GS * GROUPS) backward_warp_kernel(const Solver
                                     a.buf.counters);
 }
 
+// row-per-lane sweep (backward_cols.cuh): NX lanes per OCP, GROUPS OCPs per CTA
+template <int NX, int NU, int GROUPS>
+__global__ void __launch_bounds__(NX * GROUPS) backward_cols_kernel(const SolverArgs a, const BoxLimits<NU> lim) {
+  extern __shared__ double smem[];
+  const int w = threadIdx.x / NX;
+  const int b = blockIdx.x * GROUPS + w;
+  if (b >= a.B) return;
+  const int lane = threadIdx.x % NX;
+  const unsigned mask = ((1u << NX) - 1u) << ((threadIdx.x & 31) - lane);
+  GrpCols<NX> g{lane, mask};
+  backward_body<GrpCols<NX>, NX, NU>(g, smem + (size_t)w * ColsSmem<NX, NU>::SIZE, a, b, lim.lb, lim.ub, lim.has != 0,
+                                     a.buf.counters);
+}
+
 // CTA per OCP (nx = 28)
 template <int NX, int NU, int THREADS>
 __global__ void __launch_bounds__(THREADS, ASLR_BWD_CTA_MINB) backward_cta_kernel(const SolverArgs a, const BoxLimits<NU> lim) {
@@ -343,7 +361,13 @@ struct Launch {
     lim.has = P.has_limits;
     for (int i = 0; i < NU; ++i) lim.lb[i] = P.u_lb[i], lim.ub[i] = P.u_ub[i];
     constexpr size_t per = sizeof(double) * BwdSmem<NX, NU>::SIZE;
-    if constexpr (NX <= 12) {
+    if constexpr (NX == 8 && ASLR_BWD_COLS) {
+      constexpr int GROUPS = ASLR_BWD_COLS_GROUPS;
+      constexpr size_t slice = sizeof(double) * ColsSmem<NX, NU>::SIZE;
+      auto k = backward_cols_kernel<NX, NU, GROUPS>;
+      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(slice * GROUPS));
+      k<<<(a.B + GROUPS - 1) / GROUPS, NX * GROUPS, slice * GROUPS, s>>>(a, lim);
+    } else if constexpr (NX <= 12) {
       constexpr int GS = ASLR_BWD_GS, GROUPS = 128 / GS;
       auto k = backward_warp_kernel<NX, NU, GS, GROUPS>;
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(per * GROUPS));
