@@ -11,6 +11,11 @@
 // shared memory: the gains K (for Qxu K), the unsymmetrised Vtmp (lane j needs column j to symmetrise) and
 // the new Vxx / Vx for the next knot; Quu = Luu + (Fu^T Vxx') Fu is a butterfly sum over the lanes.
 // The next knot's record is staged into shared memory with cp.async while this knot computes.
+// Control flow is WARP-UNIFORM: the four OCPs of a warp run the sweep in lockstep and an OCP that is finished,
+// failed or out of range runs along as a ghost (loads valid data, stores nothing).  Every shuffle and barrier
+// then takes the full constant mask -- a plain SHFL / no-op instead of the WARPSYNC + divergence-check sequence
+// a partial runtime mask costs -- and the knot body is one basic block that ptxas can schedule as a whole
+// (the Cholesky chain under the Qxx products).
 // Device-only (shuffles); the host emulation keeps using backward_sweep.
 #pragma once
 
@@ -21,9 +26,10 @@ struct GrpCols {
   static constexpr int G = GS;
   static constexpr bool COLS = true;
   int lane;
-  unsigned mask;
-  __device__ __forceinline__ void sync() const { __syncwarp(mask); }
+  unsigned mask;  // the lanes of this OCP (for ballots); barriers and shuffles use the full warp
+  __device__ __forceinline__ void sync() const { __syncwarp(); }
 };
+#define ASLR_FULL 0xffffffffu
 
 template <int NX, int NU>
 struct ColsSmem {
@@ -84,17 +90,67 @@ __device__ __forceinline__ void sts_row(double* p, const double (&v)[N]) {
 }
 // sum over the G lanes of a group; every lane receives the same bits (commutative butterfly)
 template <int G>
-__device__ __forceinline__ double group_sum(unsigned mask, double v) {
+__device__ __forceinline__ double group_sum(double v) {
 #pragma unroll
-  for (int m = 1; m < G; m <<= 1) v += __shfl_xor_sync(mask, v, m);
+  for (int m = 1; m < G; m <<= 1) v += __shfl_xor_sync(ASLR_FULL, v, m);
   return v;
 }
 
-// One backward sweep with the current regularisation.  Returns false on "backward_error" (the same
-// conditions, checked at the same places, as backward_sweep).
+// Screen for "NaN, inf or >= 1e30": the high word of |v| as an integer orders like |v| itself (NaN and inf
+// have the largest exponent), so one integer max over all values followed by one compare decides whether
+// the exact test (bad_value) has to run at all.  1e30 = 0x46293E5939A08CEA.
+__device__ __forceinline__ unsigned mag_hi(double v) { return (unsigned)__double2hiint(v) & 0x7fffffffu; }
+constexpr unsigned ASLR_BAD_HI = 0x46293E59u;
+
+// cholesky<N> of vecmath.cuh with the reciprocal diagonal taken directly as rsqrt(d) (one MUFU + Newton chain
+// instead of sqrt followed by a reciprocal); same failure condition (a non-positive pivot)
+template <int N>
+__device__ __forceinline__ bool cholesky_rsqrt(double* A, double* invd) {
+  bool ok = true;
+#pragma unroll
+  for (int j = 0; j < N; ++j) {
+    double d = A[j * N + j];
+#pragma unroll
+    for (int k = 0; k < j; ++k) d -= A[j * N + k] * A[j * N + k];
+    if (d <= 0.0) ok = false;
+    const double inv = rsqrt(d);
+    invd[j] = inv;
+    A[j * N + j] = d * inv;
+#pragma unroll
+    for (int i = j + 1; i < N; ++i) {
+      double s2 = A[i * N + j];
+#pragma unroll
+      for (int k = 0; k < j; ++k) s2 -= A[i * N + k] * A[j * N + k];
+      A[i * N + j] = s2 * inv;
+    }
+  }
+  return ok;
+}
+
+// Exact zeros of the records of the soft-actuated models (knot.cuh: record_put; the same structure the
+// nx >= 16 branch of backward_sweep skips), x = [q_l q_m v_l v_m] in blocks of NQ = NX / 4:
+//   * rows q_l, v_l of Fx are zero in the columns v_m; rows q_m, v_m are zero in the columns v_l;
+//   * SEA (4 nu = nx): the link rows q_l, v_l of Fu are zero.
+// A skipped term is an exact zero, so each sum keeps the remaining terms in the same order.
+template <int NX>
+__host__ __device__ constexpr bool fx_nonzero(int k, int c) {
+  constexpr int NQ = NX / 4;
+  const bool link_row = (k < NQ) || (k >= 2 * NQ && k < 3 * NQ);
+  return link_row ? (c < 3 * NQ) : !(c >= 2 * NQ && c < 3 * NQ);
+}
 template <int NX, int NU>
-__device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const SolverArgs& a, int b, const double* u_lb,
-                                    const double* u_ub, bool box_limits, double xreg, double* sums /*[6]*/) {
+__host__ __device__ constexpr bool fu_nonzero(int k) {
+  constexpr int NQ = NX / 4;
+  return (4 * NU != NX) || (k >= NQ && k < 2 * NQ) || (k >= 3 * NQ);
+}
+
+// One backward sweep with the current regularisation, called by ALL lanes of the warp; `live` says whether
+// this lane's OCP takes part for real.  Returns false on "backward_error" (the same conditions, checked at
+// the same places, as backward_sweep); the OCP then finishes the sweep as a ghost.
+template <int NX, int NU>
+__device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const SolverArgs& a, int b, bool live,
+                                    const double* u_lb, const double* u_ub, bool box_limits, double xreg,
+                                    double* sums /*[6]*/) {
   typedef ColsSmem<NX, NU> CS;
   typedef Rec<NX, NU> RC;
   const int j = g.lane;
@@ -103,6 +159,9 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
   const AslrOcpState& st = a.buf.state[b];
   const bool feasible = st.is_feasible != 0;
   const bool use_box = box_limits && feasible && (a.opts.kind == ASLR_SOLVER_BOXDDP);
+  const bool any_box = __any_sync(ASLR_FULL, use_box && live);
+  const bool any_gaps = __any_sync(ASLR_FULL, !feasible && live);  // the gap terms are exact zeros otherwise
+  bool failed = false;
   const double* deriv = a.buf.deriv + (size_t)b * (T + 1) * RC::SIZE;
   const double* fs = a.buf.fs + (size_t)b * (T + 1) * NX;
   double stop = 0, d1 = 0, d2 = 0, dgf = 0, dqf = 0;
@@ -124,17 +183,19 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
     }
     vx += w;
     const size_t bt1 = (size_t)b * (T + 1) + T;
-    a.buf.Vx[bt1 * NX + j] = vx;
-    a.buf.Vxxfs[bt1 * NX + j] = w;
-    if (a.buf.Vxx) {
+    if (live) {
+      a.buf.Vx[bt1 * NX + j] = vx;
+      a.buf.Vxxfs[bt1 * NX + j] = w;
+      if (a.buf.Vxx) {
 #pragma unroll
-      for (int c = 0; c < NX; ++c) a.buf.Vxx[bt1 * NX * NX + j * NX + c] = vrow[c];
+        for (int c = 0; c < NX; ++c) a.buf.Vxx[bt1 * NX * NX + j * NX + c] = vrow[c];
+      }
     }
-    if (!feasible) {
-      const double fj = fs[T * NX + j];
+    if (any_gaps) {
+      const double fj = feasible ? 0.0 : fs[T * NX + j];
       const double p = vx * fj, q = fj * w;
 #pragma unroll
-      for (int k = 0; k < NX; ++k) dgf -= __shfl_sync(mask, p, k, NX), dqf += __shfl_sync(mask, q, k, NX);
+      for (int k = 0; k < NX; ++k) dgf -= __shfl_sync(ASLR_FULL, p, k, NX), dqf += __shfl_sync(ASLR_FULL, q, k, NX);
     }
     sts_row<NX>(sm + CS::VXX + j * NX, vrow);
     sm[CS::VX + j] = vx;
@@ -142,12 +203,25 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
   cp_async_drain();
   g.sync();
 
+  // output pointers of knot T - 1, this lane's element where the arrays are indexed by lane
+  double* pK = a.buf.Kgain + ((size_t)b * T + (T - 1)) * NU * NX + j;
+  double* pkff = a.buf.kff + ((size_t)b * T + (T - 1)) * NU;
+  double* pQu = a.buf.Qu + ((size_t)b * T + (T - 1)) * NU;
+  double* pQuuk = a.buf.Quuk + ((size_t)b * T + (T - 1)) * NU;
+  double* pQuu = a.buf.Quu ? a.buf.Quu + ((size_t)b * T + (T - 1)) * NU * NU : nullptr;
+  double* pVx = a.buf.Vx + ((size_t)b * (T + 1) + (T - 1)) * NX + j;
+  double* pW = a.buf.Vxxfs + ((size_t)b * (T + 1) + (T - 1)) * NX + j;
+  double* pVxx = a.buf.Vxx ? a.buf.Vxx + ((size_t)b * (T + 1) + (T - 1)) * NX * NX + j * NX : nullptr;
+  const double* psrc = deriv + (size_t)(T - 2) * RC::SIZE;  // the record staged during knot T - 1
   int cur = 0;
   for (int t = T - 1; t >= 0; --t) {
     const double* R = sm + (cur ? CS::REC1 : CS::REC0);
-    if (t >= 1) stage_record<RC::SIZE, NX>(sm + (cur ? CS::REC0 : CS::REC1), deriv + (size_t)(t - 1) * RC::SIZE, j);
+    if (t >= 1) stage_record<RC::SIZE, NX>(sm + (cur ? CS::REC0 : CS::REC1), psrc, j);
+    psrc -= RC::SIZE;
     double fsv[NX], fsj = 0.0;
-    if (!feasible) {
+#pragma unroll
+    for (int k = 0; k < NX; ++k) fsv[k] = 0.0;
+    if (any_gaps && !feasible) {
 #pragma unroll
       for (int k = 0; k < NX; ++k) fsv[k] = fs[t * NX + k];
       fsj = fs[t * NX + j];
@@ -159,7 +233,10 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
     double fu[NX][NU];  // all of Fu
 #pragma unroll
     for (int k = 0; k < NX; ++k) {
-      if constexpr (NU % 2 == 0) {
+      if (!fu_nonzero<NX, NU>(k)) {
+#pragma unroll
+        for (int i = 0; i < NU; ++i) fu[k][i] = 0.0;
+      } else if constexpr (NU % 2 == 0) {
         double r[NU];
         lds_row<NU>(R + RC::FU + k * NU, r);
 #pragma unroll
@@ -186,7 +263,8 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
     for (int i = 0; i < NU; ++i) {
       double s = 0.0;
 #pragma unroll
-      for (int k = 0; k < NX; ++k) s += fu[k][i] * vrow[k];
+      for (int k = 0; k < NX; ++k)
+        if (fu_nonzero<NX, NU>(k)) s += fu[k][i] * vrow[k];
       fuv[i] = s;
     }
     // ---- Qx[j] = Lx[j] + Fx[:,j]^T Vx', Qu = Lu + Fu^T Vx' (every lane)
@@ -202,7 +280,8 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
       for (int i = 0; i < NU; ++i) {
         double s2 = 0.0;
 #pragma unroll
-        for (int k = 0; k < NX; ++k) s2 += fu[k][i] * vxa[k];
+        for (int k = 0; k < NX; ++k)
+          if (fu_nonzero<NX, NU>(k)) s2 += fu[k][i] * vxa[k];
         qu[i] = R[RC::LU + i] + s2;
       }
     }
@@ -217,7 +296,8 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
         double f[NX];
         lds_row<NX>(R + RC::FX + k * NX, f);
 #pragma unroll
-        for (int c = 0; c < NX; ++c) s[c] += arow[k] * f[c];
+        for (int c = 0; c < NX; ++c)
+          if (fx_nonzero<NX>(k, c)) s[c] += arow[k] * f[c];
       }
       double l[NX];
       lds_row<NX>(R + RC::LXX + j * NX, l);
@@ -227,7 +307,8 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
       for (int i = 0; i < NU; ++i) {
         double s2 = 0.0;
 #pragma unroll
-        for (int k = 0; k < NX; ++k) s2 += arow[k] * fu[k][i];
+        for (int k = 0; k < NX; ++k)
+          if (fu_nonzero<NX, NU>(k)) s2 += arow[k] * fu[k][i];
         qxu[i] = R[RC::LXU + j * NU + i] + s2;
       }
     }
@@ -241,29 +322,27 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
       for (int i = 0; i < NU; ++i) {
 #pragma unroll
         for (int l = 0; l < NU; ++l) {
-          const double s = group_sum<NX>(mask, fuv[i] * fuj[l]);
+          const double s = group_sum<NX>(fuv[i] * fuj[l]);
           quu[i * NU + l] = R[RC::LUU + i * NU + l] + (s + ((i == l) ? xreg : 0.0));
         }
       }
     }
     // ---- computeGains: K[:,j] and k
     double kcol[NU], kf[NU];
-    if (!use_box) {
-      // tiny Quu: every lane factorises it (identical bits on every lane)
+    {
+      // tiny Quu: every lane factorises it (identical bits on every lane of the OCP)
       double Lc[NU * NU], Li[NU];
 #pragma unroll
       for (int r = 0; r < NU * NU; ++r) Lc[r] = quu[r];
-      const bool ok = cholesky<NU>(Lc, Li);
+      const bool ok = cholesky_rsqrt<NU>(Lc, Li);
 #pragma unroll
       for (int r = 0; r < NU; ++r) kcol[r] = qxu[r], kf[r] = qu[r];
       chol_solve<NU>(Lc, Li, kcol);
       chol_solve<NU>(Lc, Li, kf);
-      if (__any_sync(mask, !ok)) {
-        cp_async_drain();
-        return false;
-      }
-    } else {
-      if (j == 0) {
+      if (!use_box && !ok && live) failed = true, live = false;
+    }
+    if (any_box) {  // warp-uniform; the box QP itself is serial (lane 0 of each OCP that uses it)
+      if (use_box && live && j == 0) {
         double lb[NU], ub[NU], xq[NU], kinit[NU];
         bool cl[NU];
         const double* us = a.buf.us + ((size_t)b * T + t) * NU;
@@ -277,19 +356,18 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
           if (cl[r]) sm[CS::QU + r] = 0.0;
         }
       }
-      g.sync();
-      if (sm[CS::FLAG] != 0.0) {
-        cp_async_drain();
-        return false;
-      }
+      __syncwarp();
+      if (use_box && live) {
+        if (sm[CS::FLAG] != 0.0) failed = true, live = false;
 #pragma unroll
-      for (int r = 0; r < NU; ++r) {
-        kf[r] = sm[CS::KF + r];
-        qu[r] = sm[CS::QU + r];
-        double s = 0.0;
+        for (int r = 0; r < NU; ++r) {
+          kf[r] = sm[CS::KF + r];
+          qu[r] = sm[CS::QU + r];
+          double s = 0.0;
 #pragma unroll
-        for (int k = 0; k < NU; ++k) s += sm[CS::LC + r * NU + k] * qxu[k];
-        kcol[r] = s;
+          for (int k = 0; k < NU; ++k) s += sm[CS::LC + r * NU + k] * qxu[k];
+          kcol[r] = s;
+        }
       }
     }
     // ---- Quuk = Quu k ; Vx[j] = Qx[j] + K[:,j]^T Quuk - 2 K[:,j]^T Qu
@@ -329,70 +407,143 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
     // ---- symmetrise (lane j needs column j of Vtmp) + xreg, NaN / inf check
     sts_row<NX>(sm + CS::VT + j * NX, vt);
     g.sync();
-    bool bad = false;
+    unsigned mhi = 0u;
 #pragma unroll
     for (int c = 0; c < NX; ++c) {
       const double v = 0.5 * (vt[c] + sm[CS::VT + c * NX + j]) + ((c == j) ? xreg : 0.0);
       vrow[c] = v;
-      if (isnan(v) || bad_value(fabs(v))) bad = true;
+      mhi = max(mhi, mag_hi(v));
     }
     double w = 0.0;
-    if (!feasible) {
-      // ---- w = Vxx fs ; Vx += w (infeasible iterations only)
+    if (any_gaps) {
+      // ---- w = Vxx fs ; Vx += w (fs = 0 for an OCP that is feasible: w = 0 exactly)
 #pragma unroll
       for (int k = 0; k < NX; ++k) w += vrow[k] * fsv[k];
       vx += w;
     }
-    if (isnan(vx) || bad_value(fabs(vx))) bad = true;
-    if (__any_sync(mask, bad)) {
-      cp_async_drain();
-      return false;
+    mhi = max(mhi, mag_hi(vx));
+    if (__any_sync(ASLR_FULL, mhi >= ASLR_BAD_HI)) {  // rare: run the exact test
+      bool bad = isnan(vx) || bad_value(fabs(vx));
+#pragma unroll
+      for (int c = 0; c < NX; ++c) bad = bad || isnan(vrow[c]) || bad_value(fabs(vrow[c]));
+      if ((__ballot_sync(ASLR_FULL, bad) & mask) != 0u && live) failed = true, live = false;
     }
     // ---- the next knot reads Vxx, Vx from shared memory (safe: every lane is past its reads of them)
     sts_row<NX>(sm + CS::VXX + j * NX, vrow);
     sm[CS::VX + j] = vx;
-    // ---- store
-    {
-      const size_t bt = (size_t)b * T + t;
+    // ---- store (the pointers walk backwards with t)
+    if (live) {
 #pragma unroll
-      for (int r = 0; r < NU; ++r) a.buf.Kgain[bt * NU * NX + r * NX + j] = kcol[r];
+      for (int r = 0; r < NU; ++r) pK[r * NX] = kcol[r];
 #pragma unroll
       for (int r = 0; r < NU; ++r) {
         if (j == r) {
-          a.buf.kff[bt * NU + r] = kf[r];
-          a.buf.Qu[bt * NU + r] = qu[r];
-          a.buf.Quuk[bt * NU + r] = quuk[r];
+          pkff[r] = kf[r];
+          pQu[r] = qu[r];
+          pQuuk[r] = quuk[r];
         }
       }
-      if (a.buf.Quu && j == 0) {
+      if (pQuu && j == 0) {
 #pragma unroll
-        for (int e = 0; e < NU * NU; ++e) a.buf.Quu[bt * NU * NU + e] = quu[e];
+        for (int e = 0; e < NU * NU; ++e) pQuu[e] = quu[e];
       }
-      const size_t bt1 = (size_t)b * (T + 1) + t;
-      a.buf.Vx[bt1 * NX + j] = vx;
-      a.buf.Vxxfs[bt1 * NX + j] = w;
-      if (a.buf.Vxx) {
+      *pVx = vx;
+      *pW = w;
+      if (pVxx) {
 #pragma unroll
-        for (int c = 0; c < NX; ++c) a.buf.Vxx[bt1 * NX * NX + j * NX + c] = vrow[c];
+        for (int c = 0; c < NX; ++c) pVxx[c] = vrow[c];
       }
     }
+    pK -= NU * NX, pkff -= NU, pQu -= NU, pQuuk -= NU, pVx -= NX, pW -= NX;
+    if (pQuu) pQuu -= NU * NU;
+    if (pVxx) pVxx -= NX * NX;
 #pragma unroll
     for (int k = 0; k < NU; ++k) {
       stop += qu[k] * qu[k];
       d1 += qu[k] * kf[k];
       d2 -= kf[k] * quuk[k];
     }
-    if (!feasible) {
+    if (any_gaps) {
       const double p = vx * fsj, q = fsj * w;
 #pragma unroll
-      for (int k = 0; k < NX; ++k) dgf -= __shfl_sync(mask, p, k, NX), dqf += __shfl_sync(mask, q, k, NX);
+      for (int k = 0; k < NX; ++k) dgf -= __shfl_sync(ASLR_FULL, p, k, NX), dqf += __shfl_sync(ASLR_FULL, q, k, NX);
     }
     cp_async_drain();
     g.sync();
     cur ^= 1;
   }
   if (j == 0) sums[0] = stop, sums[1] = d1, sums[2] = d2, sums[3] = dgf, sums[4] = dqf;
-  return true;
+  return !failed;
+}
+
+// computeDirection() (minus calcDiff, done by K1) + expected-improvement terms, warp-uniform version of
+// backward_body: called by all lanes of the warp; b_raw may be out of range (the OCP is then a ghost).
+template <int NX, int NU>
+__device__ void backward_body_cols(const GrpCols<NX>& g, double* sm, const SolverArgs& a, int b_raw, const double* u_lb,
+                                   const double* u_ub, bool box_limits, int* n_running) {
+  typedef BwdSmem<NX, NU> SM;
+  constexpr int G = NX;
+  const int b = (b_raw < a.B) ? b_raw : a.B - 1;
+  AslrOcpState& st = a.buf.state[b];
+  bool need = (b_raw < a.B) && (st.status == ASLR_OCP_RUNNING);
+  if (!__any_sync(ASLR_FULL, need)) return;
+  const int T = a.T;
+  // ---- cost = sum of knot costs (ShootingProblem::calcDiff), ffeas = max |gap|
+  const bool rc = need && st.recalc;
+  if (__any_sync(ASLR_FULL, rc)) {
+    double c = 0.0, ff = 0.0;
+    if (rc) {
+      for (int t = g.lane; t <= T; t += G) c += a.buf.knot_cost[(size_t)b * (T + 1) + t];
+      for (int e = g.lane; e < (T + 1) * NX; e += G) ff = fmax(ff, fabs(a.buf.fs[(size_t)b * (T + 1) * NX + e]));
+    }
+    sm[SM::RED + g.lane] = c;
+    sm[SM::RED + 128 + g.lane] = ff;
+    __syncwarp();
+    if (rc && g.lane == 0) {
+      double cs = 0.0, fm = 0.0;
+      for (int l = 0; l < G; ++l) cs += sm[SM::RED + l], fm = fmax(fm, sm[SM::RED + 128 + l]);
+      st.cost = cs;
+      st.ffeas = st.is_feasible ? 0.0 : fm;
+    }
+    __syncwarp();
+  }
+  double xreg = st.xreg;
+  double sums[6];
+  int retries = 0;
+  while (__any_sync(ASLR_FULL, need)) {
+    const bool ok = backward_sweep_cols<NX, NU>(g, sm, a, b, need, u_lb, u_ub, box_limits, xreg, sums);
+    __syncwarp();
+    if (!need) continue;
+    if (ok) {
+      need = false;
+      if (g.lane == 0) {
+        st.xreg = xreg;
+        st.n_backward_retries += retries;
+        st.stop = sums[0];
+        if (a.opts.kind == ASLR_SOLVER_FDDP) {
+          st.dg = sums[1] + sums[3];
+          st.dq = sums[2] + sums[4];
+        } else {
+          st.d1 = sums[1];
+          st.d2 = sums[2];
+        }
+      }
+    } else {
+      // catch (backward_error): recalcDiff = false; increaseRegularization(); give up at reg_max
+      ++retries;
+      xreg *= a.opts.reg_incfactor;
+      if (xreg > a.opts.reg_max) xreg = a.opts.reg_max;
+      if (xreg == a.opts.reg_max) {
+        need = false;
+        if (g.lane == 0) {
+          st.xreg = xreg;
+          st.status = ASLR_OCP_REG_MAX;
+          st.n_backward_retries += retries;
+          atomicSub(n_running, 1);
+        }
+      }
+    }
+  }
 }
 
 }  // namespace aslr

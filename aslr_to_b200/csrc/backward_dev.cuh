@@ -638,12 +638,6 @@ ASLR_HD bool backward_sweep(const Grp& g, double* sm, const SolverArgs& a, int b
   return true;
 }
 
-}  // namespace aslr
-#if defined(__CUDACC__)
-#include "backward_cols.cuh"  // row-per-lane sweep for small models (device only)
-#endif
-namespace aslr {
-
 // computeDirection() (minus calcDiff, done by K1) + expected-improvement terms for one OCP
 template <class Grp, int NX, int NU>
 ASLR_HD void backward_body(const Grp& g, double* sm, const SolverArgs& a, int b, const double* u_lb,
@@ -673,13 +667,7 @@ ASLR_HD void backward_body(const Grp& g, double* sm, const SolverArgs& a, int b,
   double sums[6];
   int retries = 0;
   while (true) {
-    bool ok;
-#if defined(__CUDACC__)
-    if constexpr (Grp::COLS)
-      ok = backward_sweep_cols<NX, NU>(g, sm, a, b, u_lb, u_ub, box_limits, xreg, sums);
-    else
-#endif
-      ok = backward_sweep<Grp, NX, NU>(g, sm, a, b, u_lb, u_ub, box_limits, xreg, sums);
+    const bool ok = backward_sweep<Grp, NX, NU>(g, sm, a, b, u_lb, u_ub, box_limits, xreg, sums);
     g.sync();
     if (ok) break;
     // catch (backward_error): recalcDiff = false; increaseRegularization(); give up at reg_max
@@ -715,3 +703,7 @@ ASLR_HD void backward_body(const Grp& g, double* sm, const SolverArgs& a, int b,
 }
 
 }  // namespace aslr
+
+#if defined(__CUDACC__)
+#include "backward_cols.cuh"  // row-per-lane sweep for small models (device only)
+#endif

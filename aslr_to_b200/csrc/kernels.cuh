@@ -34,7 +34,7 @@
 #endif
 #ifndef ASLR_BWD_COLS
 #define ASLR_BWD_COLS 1         // nx = 8 backward pass: row-per-lane sweep (backward_cols.cuh), 8 lanes per OCP
-#define ASLR_BWD_COLS_GROUPS 4  // OCPs per CTA (one warp)
+#define ASLR_BWD_COLS_GROUPS 4  // OCPs per CTA (whole warps: a multiple of 32 / 8)
 #endif
 #ifndef ASLR_BWD_GS
 #define ASLR_BWD_GS 16  // lanes per OCP in the nx = 8 backward pass
@@ -271,13 +271,12 @@ template <int NX, int NU, int GROUPS>
 __global__ void __launch_bounds__(NX * GROUPS) backward_cols_kernel(const SolverArgs a, const BoxLimits<NU> lim) {
   extern __shared__ double smem[];
   const int w = threadIdx.x / NX;
-  const int b = blockIdx.x * GROUPS + w;
-  if (b >= a.B) return;
+  const int b = blockIdx.x * GROUPS + w;  // may be out of range: the body keeps whole warps in lockstep
   const int lane = threadIdx.x % NX;
   const unsigned mask = ((1u << NX) - 1u) << ((threadIdx.x & 31) - lane);
   GrpCols<NX> g{lane, mask};
-  backward_body<GrpCols<NX>, NX, NU>(g, smem + (size_t)w * ColsSmem<NX, NU>::SIZE, a, b, lim.lb, lim.ub, lim.has != 0,
-                                     a.buf.counters);
+  backward_body_cols<NX, NU>(g, smem + (size_t)w * ColsSmem<NX, NU>::SIZE, a, b, lim.lb, lim.ub, lim.has != 0,
+                             a.buf.counters);
 }
 
 // CTA per OCP (nx = 28)
