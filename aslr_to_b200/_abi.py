@@ -77,11 +77,11 @@ class OcpState(C.Structure):
     _fields_ = [(k, C.c_double) for k in ("cost", "cost_try", "stop", "xreg", "steplength", "dV", "dVexp", "d1", "d2",
                                           "dg", "dq", "ffeas")] + \
                [(k, C.c_int32) for k in ("iter", "status", "is_feasible", "was_feasible", "recalc", "accepted",
-                                         "src_slot", "n_backward_retries")]
+                                         "src_slot", "n_backward_retries", "full_steps", "reserved0")]
 
 
 OCP_STATE_DOUBLES = C.sizeof(OcpState) // 8
-assert C.sizeof(OcpState) == 12 * 8 + 8 * 4
+assert C.sizeof(OcpState) == 12 * 8 + 10 * 4
 
 
 class SolverBuffers(C.Structure):

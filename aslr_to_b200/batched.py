@@ -44,7 +44,7 @@ def decode_states(state_array):
         out[k] = raw[:, i].copy()
     ints = raw[:, len(names_d):].copy().view(np.int32).reshape(B, -1)
     for i, k in enumerate(("iter", "status", "is_feasible", "was_feasible", "recalc", "accepted", "src_slot",
-                           "n_backward_retries")):
+                           "n_backward_retries", "full_steps")):
         out[k] = ints[:, i].copy()
     return out
 

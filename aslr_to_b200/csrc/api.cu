@@ -289,7 +289,7 @@ int aslr_solve(const AslrProblem* pc, const AslrBatch* batch, const AslrSolverOp
     if (p->fn.calcdiff(p->dev, a, s) || p->fn.backward(p->dev, a, s) || p->fn.rollout(p->dev, a, s) ||
         launch_accept(a, s))
       return cuda_fail(cudaGetLastError());
-    launches += 6;  // K1, K2, K3 (rollout + two trial-cost passes), K4
+    launches += 3 + p->fn.rollout_launches;  // K1, K2, K3 (rollout phases + trial-cost passes), K4
     if ((it + 1) % poll == 0 && it + 1 < opts->maxiter) {
       const int slot = n_polls & 1;
       if (pending >= 0) {  // consume the previous poll before its slot is reused

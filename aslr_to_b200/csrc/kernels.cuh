@@ -8,8 +8,11 @@
 #include "rollout_coop.cuh"
 
 #ifndef ASLR_ROLL_THREADS
-#define ASLR_ROLL_THREADS 64  // 2-DOF rollout: CTA size and minimum resident CTAs per SM (one wave for 40960 trials)
-#define ASLR_ROLL_MINB 5
+// 2-DOF rollout: CTA size and minimum resident CTAs per SM.  32 x 8 leaves 254 registers per thread: no spills
+// on the sequential chain (64 x 5 = one wave for 40960 trials at 168 registers spilled 316 bytes per thread
+// and cost 34 us of the 277 us latency floor).
+#define ASLR_ROLL_THREADS 32
+#define ASLR_ROLL_MINB 8
 #endif
 #ifndef ASLR_K1_MINB
 #define ASLR_K1_MINB 2  // 2-DOF calc+calcDiff: minimum resident CTAs per SM (register cap 65536 / (128 * MINB))
@@ -187,10 +190,15 @@ __global__ void __launch_bounds__(128, (N <= 2) ? ASLR_K1_MINB : 1) solver_calcd
 }
 
 template <int N, int NU, bool VSA>
-__global__ void __launch_bounds__((N <= 2) ? ASLR_ROLL_THREADS : 64, (N <= 2) ? ASLR_ROLL_MINB : 1) rollout_kernel(const __grid_constant__ DevProblem<N> P, const SolverArgs a) {
-  const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__((N <= 2) ? ASLR_ROLL_THREADS : 64, (N <= 2) ? ASLR_ROLL_MINB : 1) rollout_kernel(const __grid_constant__ DevProblem<N> P, const SolverArgs a, const int phase) {
+  // threads [0, B) are the alpha = 1 trials (packed: in the steady state they are the only ones that run, see
+  // rollout_narrow), threads [B, 10 B) the other nine step lengths of each OCP; phase 1 launches only the latter
+  const long g = (long)blockIdx.x * blockDim.x + threadIdx.x + (phase == 0 ? 0 : a.B);
   if (g >= (long)a.B * ASLR_NUM_ALPHAS) return;
-  rollout_body<N, NU, VSA>(P, a, (int)(g / ASLR_NUM_ALPHAS), (int)(g % ASLR_NUM_ALPHAS));
+  const int b = (g < a.B) ? (int)g : (int)((g - a.B) / (ASLR_NUM_ALPHAS - 1));
+  const int ai = (g < a.B) ? 0 : 1 + (int)((g - a.B) % (ASLR_NUM_ALPHAS - 1));
+  if (!rollout_wanted(a, b, ai, phase)) return;
+  rollout_body<N, NU, VSA>(P, a, b, ai);
 }
 
 // K3 for the larger models: GS lanes per trial, per-knot state in shared memory (rollout_coop.cuh)
@@ -295,6 +303,7 @@ struct Launchers {
   int (*backward)(const void* P, const SolverArgs& a, cudaStream_t s);
   int (*rollout)(const void* P, const SolverArgs& a, cudaStream_t s);
   int (*quasi_static)(const void* P, const KnotArgs& a, double* us, int maxiter, double tol, cudaStream_t s);
+  int rollout_launches;  // kernels one call of `rollout` enqueues
 };
 
 inline int launch_status() { return cudaGetLastError() == cudaSuccess ? 0 : -2; }
@@ -345,8 +354,16 @@ struct Launch {
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
       k<<<(unsigned)((total + TRIALS - 1) / TRIALS), GS * TRIALS, bytes, s>>>(P, a);
     } else {
+      // two-phase speculative line search (solver_dev.cuh: rollout_wanted)
       const int threads = ASLR_ROLL_THREADS;
-      rollout_kernel<N, NU, VSA><<<(unsigned)((total + threads - 1) / threads), threads, 0, s>>>(P, a);
+      rollout_kernel<N, NU, VSA><<<(unsigned)((total + threads - 1) / threads), threads, 0, s>>>(P, a, 0);
+      if (launch_status()) return -2;
+      trial_cost_kernel<N, NU, VSA><<<(unsigned)(((long)a.B * 32 + 127) / 128), 128, 0, s>>>(P, a, 0);
+      rollout_kernel<N, NU, VSA><<<(unsigned)((total - a.B + threads - 1) / threads), threads, 0, s>>>(P, a, 1);
+      if (launch_status()) return -2;
+      trial_cost_kernel<N, NU, VSA>
+          <<<(unsigned)(((long)a.B * (ASLR_NUM_ALPHAS - 1) * 32 + 127) / 128), 128, 0, s>>>(P, a, 1);
+      return launch_status();
     }
     if (launch_status()) return -2;
     trial_cost_kernel<N, NU, VSA><<<(unsigned)(((long)a.B * 32 + 127) / 128), 128, 0, s>>>(P, a, 0);
@@ -386,7 +403,9 @@ struct Launch {
     quasi_static_kernel<N, NU, VSA><<<(unsigned)((total + 63) / 64), 64, 0, s>>>(P, a, us, maxiter, tol);
     return launch_status();
   }
-  static Launchers table() { return Launchers{&knots, &calcdiff, &backward, &rollout, &quasi_static}; }
+  static Launchers table() {
+    return Launchers{&knots, &calcdiff, &backward, &rollout, &quasi_static, (N >= ASLR_ROLLC_MINN) ? 3 : 4};
+  }
 };
 
 // defined in inst_n*.cu

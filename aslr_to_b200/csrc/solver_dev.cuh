@@ -31,6 +31,7 @@ ASLR_HD void init_body(const SolverArgs& a, int b) {
   s.d1 = 0, s.d2 = 0, s.dg = 0, s.dq = 0, s.ffeas = 0;
   s.iter = 0, s.status = ASLR_OCP_RUNNING, s.is_feasible = a.opts.is_feasible ? 1 : 0, s.was_feasible = 0;
   s.recalc = 1, s.accepted = -1, s.src_slot = -1, s.n_backward_retries = 0;
+  s.full_steps = 0, s.reserved0 = 0;
   if (b == 0) a.buf.counters[0] = a.B;
 }
 
@@ -406,6 +407,26 @@ ASLR_HD void trial_cost_finish(const SolverArgs& a, int b, int ai, double total)
   if (ai == 0 && tr[2] != 0.0 && trial_accept_test(a.buf.state[b], a.opts, 0, tr).accept) tr[3] = 1.0;
 }
 
+// Speculation policy of the forward pass (device scheduling only: the trials are independent and the line
+// search takes the first accepted one in order, so which of them are rolled out early never changes the
+// result).  An OCP that took the full step in its last ASLR_NARROW_AFTER iterations rolls out alpha = 1
+// alone (phase 0); its other step lengths follow in phase 1 only if alpha = 1 turns out not to be taken.
+// Measured on the 4096-OCP SEA batch: after iteration 9 every converging OCP takes alpha = 1 every time,
+// while the two that never converge almost never do twice in a row.
+#ifndef ASLR_NARROW_AFTER
+#define ASLR_NARROW_AFTER 2
+#endif
+ASLR_HD bool rollout_narrow(const AslrOcpState& s) { return s.full_steps >= ASLR_NARROW_AFTER; }
+// whether trial (b, ai) is rolled out in `phase` (0: before the alpha = 1 cost pass, 1: after it)
+ASLR_HD bool rollout_wanted(const SolverArgs& a, int b, int ai, int phase) {
+  const AslrOcpState& s = a.buf.state[b];
+  if (s.status != ASLR_OCP_RUNNING) return false;
+  if (ai == 0) return phase == 0;
+  const bool narrow = rollout_narrow(s);
+  if (phase == 0) return !narrow;
+  return narrow && a.buf.trial[(size_t)b * ASLR_NUM_ALPHAS * 4 + 3] == 0.0;  // alpha = 1 was not taken
+}
+
 // whether trial (b, ai) has a trajectory whose cost is wanted
 ASLR_HD bool trial_cost_wanted(const SolverArgs& a, int b, int ai) {
   if (a.buf.state[b].status != ASLR_OCP_RUNNING) return false;
@@ -454,6 +475,7 @@ ASLR_HD void accept_body(const SolverArgs& a, int b, int* n_done) {
     }
   }
   s.accepted = accepted;
+  s.full_steps = (accepted == 0) ? s.full_steps + 1 : 0;
   s.recalc = (accepted >= 0) ? 1 : 0;
   s.src_slot = accepted;
   s.steplength = steplength;

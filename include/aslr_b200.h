@@ -181,6 +181,9 @@ typedef struct AslrOcpState {
   int32_t is_feasible, was_feasible, recalc, accepted; /* accepted: alpha index of this iteration or -1 */
   int32_t src_slot;    /* trial slot K1 must adopt as the new candidate, -1 = none */
   int32_t n_backward_retries;
+  int32_t full_steps;  /* consecutive iterations that took the full step (alpha = 1); steers how many step
+                          lengths the forward pass rolls out speculatively, never the result */
+  int32_t reserved0;
 } AslrOcpState;
 
 typedef enum AslrOcpStatus {
