@@ -476,6 +476,10 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
   return !failed;
 }
 
+}  // namespace aslr
+#include "backward_rows.cuh"  // the same sweep for nx = 28: one OCP per warp
+namespace aslr {
+
 // computeDirection() (minus calcDiff, done by K1) + expected-improvement terms, warp-uniform version of
 // backward_body: called by all lanes of the warp; b_raw may be out of range (the OCP is then a ghost).
 template <int NX, int NU>
@@ -511,7 +515,11 @@ __device__ void backward_body_cols(const GrpCols<NX>& g, double* sm, const Solve
   double sums[6];
   int retries = 0;
   while (__any_sync(ASLR_FULL, need)) {
-    const bool ok = backward_sweep_cols<NX, NU>(g, sm, a, b, need, u_lb, u_ub, box_limits, xreg, sums);
+    bool ok;
+    if constexpr (NX > 16)
+      ok = backward_sweep_rows<NX, NU>(g, sm, a, b, need, xreg, sums);  // no box QP: see the launcher
+    else
+      ok = backward_sweep_cols<NX, NU>(g, sm, a, b, need, u_lb, u_ub, box_limits, xreg, sums);
     __syncwarp();
     if (!need) continue;
     if (ok) {

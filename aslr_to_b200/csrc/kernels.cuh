@@ -39,6 +39,10 @@
 #define ASLR_BWD_COLS 1         // nx = 8 backward pass: row-per-lane sweep (backward_cols.cuh), 8 lanes per OCP
 #define ASLR_BWD_COLS_GROUPS 4  // OCPs per CTA (whole warps: a multiple of 32 / 8)
 #endif
+#ifndef ASLR_BWD_ROWS
+#define ASLR_BWD_ROWS 1       // nx = 28, nu <= 8 backward pass: row-per-lane sweep, one OCP per warp (backward_rows.cuh)
+#define ASLR_BWD_ROWS_MINB 7  // resident CTAs (= OCPs) per SM: 31.6 KB of shared memory each
+#endif
 #ifndef ASLR_BWD_GS
 #define ASLR_BWD_GS 16  // lanes per OCP in the nx = 8 backward pass
 #endif
@@ -287,6 +291,15 @@ __global__ void __launch_bounds__(NX * GROUPS) backward_cols_kernel(const Solver
                              a.buf.counters);
 }
 
+// row-per-lane sweep for nx = 28 (backward_rows.cuh): one warp = one OCP = one CTA
+template <int NX, int NU>
+__global__ void __launch_bounds__(32, ASLR_BWD_ROWS_MINB) backward_rows_kernel(const SolverArgs a) {
+  extern __shared__ double smem[];
+  const int lane = threadIdx.x;
+  GrpCols<NX> g{lane, (NX == 32) ? 0xffffffffu : ((1u << NX) - 1u)};
+  backward_body_cols<NX, NU>(g, smem, a, (int)blockIdx.x, nullptr, nullptr, false, a.buf.counters);
+}
+
 // CTA per OCP (nx = 28)
 template <int NX, int NU, int THREADS>
 __global__ void __launch_bounds__(THREADS, ASLR_BWD_CTA_MINB) backward_cta_kernel(const SolverArgs a, const BoxLimits<NU> lim) {
@@ -383,6 +396,19 @@ struct Launch {
       auto k = backward_cols_kernel<NX, NU, GROUPS>;
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(slice * GROUPS));
       k<<<(a.B + GROUPS - 1) / GROUPS, NX * GROUPS, slice * GROUPS, s>>>(a, lim);
+    } else if constexpr (NX > 16 && NX <= 32 && NU <= 8 && ASLR_BWD_ROWS) {
+      // (the box QP of SolverBoxDDP stays with the CTA-per-OCP sweep)
+      if (!(a.opts.kind == ASLR_SOLVER_BOXDDP && P.has_limits)) {
+        constexpr size_t bytes = sizeof(double) * RowsSmem<NX, NU>::SIZE;
+        auto k = backward_rows_kernel<NX, NU>;
+        cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        k<<<a.B, 32, bytes, s>>>(a);
+        return launch_status();
+      }
+      constexpr int THREADS = ASLR_BWD_CTA_THREADS;
+      auto k = backward_cta_kernel<NX, NU, THREADS>;
+      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)per);
+      k<<<a.B, THREADS, per, s>>>(a, lim);
     } else if constexpr (NX <= 12) {
       constexpr int GS = ASLR_BWD_GS, GROUPS = 128 / GS;
       auto k = backward_warp_kernel<NX, NU, GS, GROUPS>;
