@@ -105,26 +105,53 @@ constexpr unsigned ASLR_BAD_HI = 0x46293E59u;
 // cholesky<N> of vecmath.cuh with the reciprocal diagonal taken directly as rsqrt(d) (one MUFU + Newton chain
 // instead of sqrt followed by a reciprocal); same failure condition (a non-positive pivot)
 template <int N>
-__device__ __forceinline__ bool cholesky_rsqrt(double* A, double* invd) {
+__device__ __forceinline__ bool cholesky_rsqrt(double (&A)[N * N], double (&invd)[N]) {
+  // every loop has the fixed trip count N with a compile-time guard: triangular trip counts nested three deep
+  // were left rolled for N = 7, which put the matrix in local memory
   bool ok = true;
 #pragma unroll
   for (int j = 0; j < N; ++j) {
     double d = A[j * N + j];
 #pragma unroll
-    for (int k = 0; k < j; ++k) d -= A[j * N + k] * A[j * N + k];
+    for (int k = 0; k < N; ++k)
+      if (k < j) d -= A[j * N + k] * A[j * N + k];
     if (d <= 0.0) ok = false;
     const double inv = rsqrt(d);
     invd[j] = inv;
     A[j * N + j] = d * inv;
 #pragma unroll
-    for (int i = j + 1; i < N; ++i) {
-      double s2 = A[i * N + j];
+    for (int i = 0; i < N; ++i) {
+      if (i > j) {
+        double s2 = A[i * N + j];
 #pragma unroll
-      for (int k = 0; k < j; ++k) s2 -= A[i * N + k] * A[j * N + k];
-      A[i * N + j] = s2 * inv;
+        for (int k = 0; k < N; ++k)
+          if (k < j) s2 -= A[i * N + k] * A[j * N + k];
+        A[i * N + j] = s2 * inv;
+      }
     }
   }
   return ok;
+}
+// chol_solve<N> of vecmath.cuh in the same fixed-trip-count form
+template <int N>
+__device__ __forceinline__ void chol_solve_regs(const double (&L)[N * N], const double (&invd)[N], double (&b)[N]) {
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    double s = b[i];
+#pragma unroll
+    for (int k = 0; k < N; ++k)
+      if (k < i) s -= L[i * N + k] * b[k];
+    b[i] = s * invd[i];
+  }
+#pragma unroll
+  for (int ii = 0; ii < N; ++ii) {
+    const int i = N - 1 - ii;
+    double s = b[i];
+#pragma unroll
+    for (int k = 0; k < N; ++k)
+      if (k > i) s -= L[k * N + i] * b[k];
+    b[i] = s * invd[i];
+  }
 }
 
 // Exact zeros of the records of the soft-actuated models (knot.cuh: record_put; the same structure the
@@ -337,8 +364,8 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
       const bool ok = cholesky_rsqrt<NU>(Lc, Li);
 #pragma unroll
       for (int r = 0; r < NU; ++r) kcol[r] = qxu[r], kf[r] = qu[r];
-      chol_solve<NU>(Lc, Li, kcol);
-      chol_solve<NU>(Lc, Li, kf);
+      chol_solve_regs<NU>(Lc, Li, kcol);
+      chol_solve_regs<NU>(Lc, Li, kf);
       if (!use_box && !ok && live) failed = true, live = false;
     }
     if (any_box) {  // warp-uniform; the box QP itself is serial (lane 0 of each OCP that uses it)

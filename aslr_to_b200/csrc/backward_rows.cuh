@@ -14,6 +14,9 @@
 //   * one record buffer (16 KB): the next record is fetched with cp.async as soon as the last read of this one
 //     (the Quu entries) is done, under the Cholesky / gains / exchanges of this knot;
 //   * shared memory per OCP = 31.6 KB -> 7 OCPs per SM, one wave for 1024 OCPs.
+//   * the gap terms of FDDP's expected improvement (dg, dq: sums over the knot of Vx.fs and fs.Vxx fs) are
+//     butterfly sums over the lanes, not the sequential k = 0..NX-1 sum of backward_sweep (28 ordered shuffles
+//     per term and knot cost more than the Cholesky); the difference is one rounding of a sum of 28 terms.
 // Device-only; included from backward_cols.cuh's users (kernels.cuh).  Same recursion and failure semantics as
 // backward_sweep (backward_dev.cuh); the summation order of each dot product is the dense order with the
 // exact-zero terms of Fx / Fu skipped (fx_nonzero / fu_nonzero).
@@ -38,6 +41,28 @@ struct RowsSmem {
   static constexpr int SIZE = (END > RED_END) ? END : RED_END;
 };
 
+// rows k of block BLK (q_l, q_m, v_l or v_m) of  Qxx[j,:] += A[j][k] Fx[k,:]  and  Qxu[j,:] += A[j][k] Fu[k,:];
+// the exact-zero pattern of Fx / Fu depends on the block only, so the k loop can stay rolled
+template <int NX, int NU, int BLK>
+__device__ __forceinline__ void qxx_block(const double* R, const double* AT, int j, double (&qxx)[NX],
+                                          double (&qxu)[NU]) {
+  typedef Rec<NX, NU> RC;
+  constexpr int NQ = NX / 4, K0 = BLK * NQ;
+#pragma unroll 1
+  for (int k = K0; k < K0 + NQ; ++k) {
+    const double aj = AT[k * NX + j];
+    double f[NX];
+    lds_row<NX>(R + RC::FX + k * NX, f);
+#pragma unroll
+    for (int c = 0; c < NX; ++c)
+      if (fx_nonzero<NX>(K0, c)) qxx[c] += aj * f[c];
+    if (fu_nonzero<NX, NU>(K0)) {
+#pragma unroll
+      for (int i = 0; i < NU; ++i) qxu[i] += aj * R[RC::FU + k * NU + i];
+    }
+  }
+}
+
 template <int NX, int NU>
 __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const SolverArgs& a, int b, bool live,
                                     double xreg, double* sums /*[6]*/) {
@@ -52,7 +77,7 @@ __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const Solv
   const int T = a.T;
   const AslrOcpState& st = a.buf.state[b];
   const bool feasible = st.is_feasible != 0;
-  const bool any_gaps = !feasible && live;  // warp-uniform: one OCP per warp
+  const bool any_gaps = __any_sync(ASLR_FULL, !feasible && live);  // one OCP per warp: uniform, and the vote tells ptxas so
   const double* deriv = a.buf.deriv + (size_t)b * (T + 1) * RC::SIZE;
   const double* fs = a.buf.fs + (size_t)b * (T + 1) * NX;
   double stop = 0, d1 = 0, d2 = 0, dgf = 0, dqf = 0;
@@ -85,9 +110,7 @@ __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const Solv
     }
     if (any_gaps) {
       const double fj = fs[T * NX + j];
-      const double p = vx * fj, q = fj * w;
-#pragma unroll
-      for (int k = 0; k < NX; ++k) dgf -= __shfl_sync(ASLR_FULL, p, k), dqf += __shfl_sync(ASLR_FULL, q, k);
+      dgf -= group_sum<32>(pad ? 0.0 : vx * fj), dqf += group_sum<32>(pad ? 0.0 : fj * w);
     }
     if (!pad) {
       sts_row<NX>(sm + CS::VXX + j * NX, vrow);
@@ -111,25 +134,22 @@ __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const Solv
     double fsj = 0.0;
     if (any_gaps) fsj = fs[t * NX + j];
     // ---- A[j,:] = sum_k Fx[k][j] Vxx'[k,:] ; Qx[j] = Lx[j] + Fx[:,j]^T Vx'
+    // (k loops are rolled: the fully unrolled knot body was ~4300 instructions = 68 KB, and seven warps at
+    //  different places of it made instruction fetch the top stall reason)
     double arow[NX], qx;
     {
-      double fxc[NX];  // column j of Fx
-#pragma unroll
-      for (int k = 0; k < NX; ++k) fxc[k] = R[RC::FX + k * NX + j];
 #pragma unroll
       for (int c = 0; c < NX; ++c) arow[c] = 0.0;
-#pragma unroll
+      double s = 0.0;
+#pragma unroll 2
       for (int k = 0; k < NX; ++k) {
+        const double f = R[RC::FX + k * NX + j];
         double v[NX];
         lds_row<NX>(sm + CS::VXX + k * NX, v);
 #pragma unroll
-        for (int c = 0; c < NX; ++c) arow[c] += fxc[k] * v[c];
+        for (int c = 0; c < NX; ++c) arow[c] += f * v[c];
+        s += f * sm[CS::VX + k];
       }
-      double vxa[NX];
-      lds_row<NX>(sm + CS::VX, vxa);
-      double s = 0.0;
-#pragma unroll
-      for (int k = 0; k < NX; ++k) s += fxc[k] * vxa[k];
       qx = R[RC::LX + j] + s;
     }
     // ---- FuV[:,j] = sum_k Fu[k][:] Vxx'[k][j] (own row, by symmetry) -> shared memory for the Quu entries
@@ -162,31 +182,29 @@ __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const Solv
       for (int r = 0; r < NU; ++r) qu[r] = __shfl_sync(ASLR_FULL, mine, r);
     }
     // ---- Qxx[j,:] = Lxx[j,:] + A[j,:] Fx, Qxu[j,:] = Lxu[j,:] + A[j,:] Fu
+    // A[j][k] has to be indexed by the loop variable: park the row in shared memory, transposed (element
+    // (k, lane) -> conflict-free), on top of Vxx', which nobody reads any more once every lane is here
     double qxx[NX], qxu[NU];
     {
+      __syncwarp();
+      double* AT = sm + CS::VXX;
+      if (!pad) {
+#pragma unroll
+        for (int c = 0; c < NX; ++c) AT[c * NX + j] = arow[c];
+      }
+      __syncwarp();
 #pragma unroll
       for (int c = 0; c < NX; ++c) qxx[c] = 0.0;
 #pragma unroll
-      for (int k = 0; k < NX; ++k) {
-        double f[NX];
-        lds_row<NX>(R + RC::FX + k * NX, f);
-#pragma unroll
-        for (int c = 0; c < NX; ++c)
-          if (fx_nonzero<NX>(k, c)) qxx[c] += arow[k] * f[c];
-      }
+      for (int i = 0; i < NU; ++i) qxu[i] = 0.0;
+      qxx_block<NX, NU, 0>(R, AT, j, qxx, qxu);
+      qxx_block<NX, NU, 1>(R, AT, j, qxx, qxu);
+      qxx_block<NX, NU, 2>(R, AT, j, qxx, qxu);
+      qxx_block<NX, NU, 3>(R, AT, j, qxx, qxu);
       double l[NX];
       lds_row<NX>(R + RC::LXX + j * NX, l);
 #pragma unroll
       for (int c = 0; c < NX; ++c) qxx[c] = l[c] + qxx[c];
-#pragma unroll
-      for (int i = 0; i < NU; ++i) qxu[i] = 0.0;
-#pragma unroll
-      for (int k = 0; k < NX; ++k) {
-        if (fu_nonzero<NX, NU>(k)) {
-#pragma unroll
-          for (int i = 0; i < NU; ++i) qxu[i] += arow[k] * R[RC::FU + k * NU + i];
-        }
-      }
 #pragma unroll
       for (int i = 0; i < NU; ++i) qxu[i] = R[RC::LXU + j * NU + i] + qxu[i];
     }
@@ -214,12 +232,12 @@ __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const Solv
 #pragma unroll
       for (int r = 0; r < NU; ++r)
 #pragma unroll
-        for (int c = 0; c <= r; ++c) Lc[r * NU + c] = sm[CS::QUU + r * NU + c];
+        for (int c = 0; c < NU; ++c) Lc[r * NU + c] = (c <= r) ? sm[CS::QUU + r * NU + c] : 0.0;
       const bool ok = cholesky_rsqrt<NU>(Lc, Li);
 #pragma unroll
       for (int r = 0; r < NU; ++r) kcol[r] = qxu[r], kf[r] = qu[r];
-      chol_solve<NU>(Lc, Li, kcol);
-      chol_solve<NU>(Lc, Li, kf);
+      chol_solve_regs<NU>(Lc, Li, kcol);
+      chol_solve_regs<NU>(Lc, Li, kf);
       if (!ok) {  // one OCP per warp: the failure is warp-uniform, give up at once like backward_sweep
         cp_async_drain();
         return false;
@@ -327,9 +345,7 @@ __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const Solv
       d2 -= kf[k] * quuk[k];
     }
     if (any_gaps) {
-      const double p = vx * fsj, q = fsj * w;
-#pragma unroll
-      for (int k = 0; k < NX; ++k) dgf -= __shfl_sync(ASLR_FULL, p, k), dqf += __shfl_sync(ASLR_FULL, q, k);
+      dgf -= group_sum<32>(pad ? 0.0 : vx * fsj), dqf += group_sum<32>(pad ? 0.0 : fsj * w);
     }
     cp_async_drain();
     __syncwarp();
