@@ -48,7 +48,7 @@ __device__ __forceinline__ void qxx_block(const double* R, const double* AT, int
                                           double (&qxu)[NU]) {
   typedef Rec<NX, NU> RC;
   constexpr int NQ = NX / 4, K0 = BLK * NQ;
-#pragma unroll 1
+#pragma unroll
   for (int k = K0; k < K0 + NQ; ++k) {
     const double aj = AT[k * NX + j];
     double f[NX];
@@ -141,7 +141,7 @@ __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const Solv
 #pragma unroll
       for (int c = 0; c < NX; ++c) arow[c] = 0.0;
       double s = 0.0;
-#pragma unroll 2
+#pragma unroll 4
       for (int k = 0; k < NX; ++k) {
         const double f = R[RC::FX + k * NX + j];
         double v[NX];

@@ -208,18 +208,22 @@ __global__ void __launch_bounds__((N <= 2) ? ASLR_ROLL_THREADS : 64, (N <= 2) ? 
 // K3 for the larger models: GS lanes per trial, per-knot state in shared memory (rollout_coop.cuh)
 template <int N, int NU, bool VSA, int GS, int TRIALS>
 __global__ void __launch_bounds__(GS * TRIALS, ASLR_ROLLC_MINB) rollout_coop_kernel(const __grid_constant__ DevProblem<N> P,
-                                                                                    const SolverArgs a) {
+                                                                                    const SolverArgs a, const int phase) {
   extern __shared__ double smem[];
   for (int i = threadIdx.x; i < N; i += blockDim.x) model_const_fill<N>(P, smem, i);
   __syncthreads();
   const int w = threadIdx.x / GS;
-  const long trial = (long)blockIdx.x * TRIALS + w;
+  // trials [0, B) are alpha = 1 of every OCP, [B, 10 B) the other step lengths (see rollout_kernel / rollout_wanted)
+  const long trial = (long)blockIdx.x * TRIALS + w + (phase <= 0 ? 0 : a.B);
   if (trial >= (long)a.B * ASLR_NUM_ALPHAS) return;
+  const int b = (trial < a.B) ? (int)trial : (int)((trial - a.B) / (ASLR_NUM_ALPHAS - 1));
+  const int ai = (trial < a.B) ? 0 : 1 + (int)((trial - a.B) % (ASLR_NUM_ALPHAS - 1));
+  if (!rollout_wanted(a, b, ai, phase)) return;
   const int lane = threadIdx.x % GS;
   const unsigned mask = (GS == 32) ? 0xffffffffu : (((1u << GS) - 1u) << ((threadIdx.x & 31) - lane));
   GrpSub<GS> g{lane, mask};
   rollout_coop_body<GrpSub<GS>, N, NU, VSA>(g, smem + ModelConst<N>::SIZE + (size_t)w * RollSmem<N, NU>::SIZE, smem, P, a,
-                                            (int)(trial / ASLR_NUM_ALPHAS), (int)(trial % ASLR_NUM_ALPHAS));
+                                            b, ai);
 }
 
 // K3b: one warp per trial; lanes take the knots 32 at a time, the costs are then added in knot order
@@ -365,7 +369,12 @@ struct Launch {
       constexpr size_t bytes = sizeof(double) * (ModelConst<N>::SIZE + (size_t)TRIALS * RollSmem<N, NU>::SIZE);
       auto k = rollout_coop_kernel<N, NU, VSA, GS, TRIALS>;
       cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-      k<<<(unsigned)((total + TRIALS - 1) / TRIALS), GS * TRIALS, bytes, s>>>(P, a);
+      k<<<(unsigned)((total + TRIALS - 1) / TRIALS), GS * TRIALS, bytes, s>>>(P, a, -1);
+      if (launch_status()) return -2;
+      trial_cost_kernel<N, NU, VSA><<<(unsigned)(((long)a.B * 32 + 127) / 128), 128, 0, s>>>(P, a, 0);
+      trial_cost_kernel<N, NU, VSA>
+          <<<(unsigned)(((long)a.B * (ASLR_NUM_ALPHAS - 1) * 32 + 127) / 128), 128, 0, s>>>(P, a, 1);
+      return launch_status();
     } else {
       // two-phase speculative line search (solver_dev.cuh: rollout_wanted)
       const int threads = ASLR_ROLL_THREADS;
@@ -378,11 +387,6 @@ struct Launch {
           <<<(unsigned)(((long)a.B * (ASLR_NUM_ALPHAS - 1) * 32 + 127) / 128), 128, 0, s>>>(P, a, 1);
       return launch_status();
     }
-    if (launch_status()) return -2;
-    trial_cost_kernel<N, NU, VSA><<<(unsigned)(((long)a.B * 32 + 127) / 128), 128, 0, s>>>(P, a, 0);
-    trial_cost_kernel<N, NU, VSA>
-        <<<(unsigned)(((long)a.B * (ASLR_NUM_ALPHAS - 1) * 32 + 127) / 128), 128, 0, s>>>(P, a, 1);
-    return launch_status();
   }
   static int backward(const void* Pv, const SolverArgs& a, cudaStream_t s) {
     const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);

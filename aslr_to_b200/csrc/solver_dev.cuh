@@ -417,10 +417,13 @@ ASLR_HD void trial_cost_finish(const SolverArgs& a, int b, int ai, double total)
 #define ASLR_NARROW_AFTER 2
 #endif
 ASLR_HD bool rollout_narrow(const AslrOcpState& s) { return s.full_steps >= ASLR_NARROW_AFTER; }
-// whether trial (b, ai) is rolled out in `phase` (0: before the alpha = 1 cost pass, 1: after it)
+// whether trial (b, ai) is rolled out in `phase` (0: before the alpha = 1 cost pass, 1: after it, -1: there is
+// only one phase -- the lane-cooperative 7-DOF rollout, whose latency floor equals its full-batch time
+// (3.6 ms either way), so a second phase can only add to it: measured 83.6 -> 98.5 ms per MPC step)
 ASLR_HD bool rollout_wanted(const SolverArgs& a, int b, int ai, int phase) {
   const AslrOcpState& s = a.buf.state[b];
   if (s.status != ASLR_OCP_RUNNING) return false;
+  if (phase < 0) return true;  // single-phase launch: all step lengths at once
   if (ai == 0) return phase == 0;
   const bool narrow = rollout_narrow(s);
   if (phase == 0) return !narrow;
