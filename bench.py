@@ -33,7 +33,7 @@ METRIC = "batched_fddp_ocp_iters_per_s"
 UNIT = "OCP-iterations/s"
 B_PER_GPU = 4096
 SEED = 20240001
-K1_DRAM_TRAFFIC_PER_LAUNCH = 773.4e6  # dram__bytes_read + write of one knot_kernel launch, ncu --set full (profiles/r01b_ncu_full.md)
+K1_DRAM_TRAFFIC_PER_LAUNCH = 785.1e6  # dram__bytes_read + write of one knot_kernel launch, ncu --set full (profiles/r01e_ncu_full.md)
 ALGO_BYTES_PER_KNOT = 1544  # 2-DOF SEA, read x,u; write xnext,cost,Fx,Fu,Lx,Lu,Lxx,Lxu,Luu
 
 
@@ -329,10 +329,10 @@ def run_ours(args):
               "share": dict(zip(STAGES, [round(float(v / stage_ms.sum()), 3) for v in stage_ms])),
               "full_batch_us": dict(zip(STAGES, [float(v) for v in rows[1]])),
               "floor_us": dict(zip(STAGES, [float(v) for v in rows[-1]])),
-              "fp64_pipe_frac_ncu": {"calcdiff": 0.25, "backward": 0.20, "rollout": 0.41},
+              "fp64_pipe_frac_ncu": {"calcdiff": 0.26, "backward": 0.21, "rollout": 0.18},
               "note": "stepwise ABI with one event pair and one sync per stage, after the timed region; full_batch = "
                       "iteration 1, floor = last iteration (stragglers only); FP64-pipe utilisation of each kernel at "
-                      "full batch from profiles/r01c_ncu_full.md (measured FP64 peak 34.2 TFLOP/s)"}
+                      "full batch from profiles/r01e_ncu_full.md (rollout: the alpha = 1 phase of a mid-solve iteration; measured FP64 peak 34.2 TFLOP/s)"}
 
     if rank == 0:
         line = {
@@ -350,7 +350,7 @@ def run_ours(args):
                          "bound": "hbm", "achieved": achieved, "peak": peak,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                          "unit": "GB/s", "frac": achieved / peak, "traffic": K1_DRAM_TRAFFIC_PER_LAUNCH,
-                         "traffic_source": "ncu --set full capture of this kernel, profiles/r01b_ncu_full.md",
+                         "traffic_source": "ncu --set full capture of this kernel, profiles/r01e_ncu_full.md",
                          "fp64": {"dfma_latency_cycles": 8.2, "peak_tflops_measured": 34.2,
                                   "source": "tools/fp64_peak.cu on this pool, profiles/r01b_fp64_peak.json"}},
             "clocks": clocks, "stages": stages,
