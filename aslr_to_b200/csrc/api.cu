@@ -1,6 +1,7 @@
 // extern "C" boundary of libaslr_b200.so (see include/aslr_b200.h for the contract of every entry).
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -54,6 +55,17 @@ int launch_accept(const SolverArgs& a, cudaStream_t s) {
 }
 }  // namespace aslr
 
+// aslr_solve splits the batch into sub-batches that run the same kernel sequence on their own streams (see
+// aslr_solve); counters[k] is the "still running" word of sub-batch k (AslrSolverBuffers.counters holds 4 ints)
+#define ASLR_MAX_LANES 4
+#ifndef ASLR_SOLVE_LANES
+#define ASLR_SOLVE_LANES 4
+#endif
+#ifndef ASLR_LANE_MIN_OCPS
+#define ASLR_LANE_MIN_OCPS 1024  // smallest sub-batch worth a stream of its own (measured: 4 x 1024 OCPs of the
+                                 // 2-DOF batch 59.2 -> 56.8 ms; 4 x 256 OCPs of the 7-DOF batch 83.8 -> 84.8 ms)
+#endif
+
 struct AslrProblem {
   AslrProblemDesc desc;
   int n, nx, nu;
@@ -61,8 +73,12 @@ struct AslrProblem {
   Launchers fn;
   // DevProblem<N> for the instantiated N (largest is N = 7)
   alignas(16) unsigned char dev[sizeof(DevProblem<ASLR_MAX_DOF>)];
-  int* pinned_counter;  // host-pinned mirror of counters[0] used by aslr_solve (two poll slots)
-  cudaEvent_t poll_event[2];
+  // aslr_solve: host-pinned mirrors of the "OCPs still running" words (two poll slots per sub-batch) and the
+  // streams / events of the sub-batch pipeline
+  int* pinned_counter;
+  cudaEvent_t poll_event[2 * ASLR_MAX_LANES];
+  cudaStream_t lane_stream[ASLR_MAX_LANES];  // [0] unused: sub-batch 0 runs on the caller's stream
+  cudaEvent_t fork_event, join_event[ASLR_MAX_LANES];
 };
 
 extern "C" {
@@ -127,7 +143,9 @@ int aslr_problem_create(const AslrProblemDesc* desc, AslrProblem** out) {
   p->nu = desc->dyn.nu;
   p->vsa = vsa;
   p->pinned_counter = nullptr;
-  p->poll_event[0] = p->poll_event[1] = nullptr;
+  p->fork_event = nullptr;
+  for (int k = 0; k < 2 * ASLR_MAX_LANES; ++k) p->poll_event[k] = nullptr;
+  for (int k = 0; k < ASLR_MAX_LANES; ++k) p->lane_stream[k] = nullptr, p->join_event[k] = nullptr;
   std::memset(p->dev, 0, sizeof(p->dev));
   if (n == 2) {
     fill_dev_problem<2>(*desc, *reinterpret_cast<DevProblem<2>*>(p->dev));
@@ -146,8 +164,13 @@ int aslr_problem_create(const AslrProblemDesc* desc, AslrProblem** out) {
 int aslr_problem_destroy(AslrProblem* p) {
   if (p) {
     if (p->pinned_counter) cudaFreeHost(p->pinned_counter);
-    for (int k = 0; k < 2; ++k)
+    for (int k = 0; k < 2 * ASLR_MAX_LANES; ++k)
       if (p->poll_event[k]) cudaEventDestroy(p->poll_event[k]);
+    if (p->fork_event) cudaEventDestroy(p->fork_event);
+    for (int k = 0; k < ASLR_MAX_LANES; ++k) {
+      if (p->join_event[k]) cudaEventDestroy(p->join_event[k]);
+      if (p->lane_stream[k]) cudaStreamDestroy(p->lane_stream[k]);
+    }
     delete p;
   }
   return ASLR_OK;
@@ -258,62 +281,140 @@ int aslr_accept_step(const AslrProblem* p, const AslrBatch* batch, const AslrSol
   return ASLR_OK;
 }
 
+// the OCPs [b0, b0 + nb) of a batch as a batch of their own (every array is OCP-major)
+static SolverArgs sub_batch(const SolverArgs& a, const AslrProblem* p, int b0, int nb, int lane) {
+  SolverArgs r = a;
+  const size_t T = a.T, nx = p->nx, nu = p->nu, n = p->n, rec = aslr_record_doubles(p->nx, p->nu);
+  const size_t o = (size_t)b0;
+  r.B = nb;
+  r.x0 = a.x0 + o * nx;
+  if (a.K_ocp) r.K_ocp = a.K_ocp + o * n * n;
+  if (a.mref_ocp) r.mref_ocp = a.mref_ocp + o * 12;
+  AslrSolverBuffers& q = r.buf;
+  q.xs += o * (T + 1) * nx, q.us += o * T * nu, q.xnext += o * T * nx, q.knot_cost += o * (T + 1);
+  q.deriv += o * (T + 1) * rec, q.fs += o * (T + 1) * nx, q.Kgain += o * T * nu * nx, q.kff += o * T * nu;
+  q.Vx += o * (T + 1) * nx, q.Vxxfs += o * (T + 1) * nx, q.Qu += o * T * nu, q.Quuk += o * T * nu;
+  if (q.Vxx) q.Vxx += o * (T + 1) * nx * nx;
+  if (q.Quu) q.Quu += o * T * nu * nu;
+  q.xs_try += o * ASLR_NUM_ALPHAS * (T + 1) * nx, q.us_try += o * ASLR_NUM_ALPHAS * T * nu;
+  q.trial += o * ASLR_NUM_ALPHAS * 4;
+  if (q.log) q.log += o * (size_t)a.opts.maxiter * ASLR_LOG_FIELDS;
+  q.state += o;
+  q.counters += lane;
+  return r;
+}
+
+// Sub-batch pipeline.  One iteration is a chain of kernels of very different character: K1 and (at full batch)
+// K2 are throughput kernels, while K3 -- one thread per trial running T sequential knots -- leaves most of the
+// GPU idle for its whole duration, and nothing of an OCP's iteration can overlap with anything else of the same
+// OCP (K3 -> K4 -> K1 -> K2 -> K3).  OCPs are independent, though: the batch is cut into ASLR_SOLVE_LANES
+// contiguous sub-batches, each with its own stream, "still running" word and poll slots, so the latency-bound
+// stage of one sub-batch runs under the throughput-bound stages of the others.  Results do not depend on the
+// cut (no kernel looks across OCPs).  Measured gain is modest (4 %): the chains that now overlap with K1 / K2
+// of other sub-batches share issue slots and the FP64 pipe with them and get slower themselves.
+// ASLR_SOLVE_LANES in the environment overrides the number of sub-batches (1 = the single-stream sequence).
 int aslr_solve(const AslrProblem* pc, const AslrBatch* batch, const AslrSolverOpts* opts, const AslrSolverBuffers* buf,
                AslrSolveResult* result, void* stream) {
   AslrProblem* p = const_cast<AslrProblem*>(pc);
   SolverArgs a;
   if (int rc = make_args(p, batch, opts, buf, 0, &a)) return rc;
   cudaStream_t s = (cudaStream_t)stream;
+  int L = ASLR_SOLVE_LANES;
+  if (const char* ev = getenv("ASLR_SOLVE_LANES")) L = atoi(ev);
+  if (L > ASLR_MAX_LANES) L = ASLR_MAX_LANES;
+  int min_ocps = ASLR_LANE_MIN_OCPS;
+  if (const char* ev = getenv("ASLR_LANE_MIN_OCPS")) min_ocps = atoi(ev);
+  if (min_ocps < 1) min_ocps = 1;
+  while (L > 1 && batch->B / L < min_ocps) --L;
+  if (L < 1) L = 1;
   if (!p->pinned_counter) {
-    cudaError_t e = cudaMallocHost((void**)&p->pinned_counter, 4 * sizeof(int));
+    cudaError_t e = cudaMallocHost((void**)&p->pinned_counter, 2 * ASLR_MAX_LANES * sizeof(int));
+    if (e != cudaSuccess) return cuda_fail(e);
+    for (int k = 0; k < 2 * ASLR_MAX_LANES && e == cudaSuccess; ++k)
+      e = cudaEventCreateWithFlags(&p->poll_event[k], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->fork_event, cudaEventDisableTiming);
+    for (int k = 1; k < ASLR_MAX_LANES && e == cudaSuccess; ++k) {
+      e = cudaStreamCreateWithFlags(&p->lane_stream[k], cudaStreamNonBlocking);
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->join_event[k], cudaEventDisableTiming);
+    }
+    if (e != cudaSuccess) return cuda_fail(e);
+  }
+  SolverArgs la[ASLR_MAX_LANES];
+  cudaStream_t ls[ASLR_MAX_LANES];
+  for (int k = 0; k < L; ++k) {
+    const int b0 = (int)((long)batch->B * k / L), b1 = (int)((long)batch->B * (k + 1) / L);
+    la[k] = sub_batch(a, p, b0, b1 - b0, k);
+    ls[k] = (k == 0) ? s : p->lane_stream[k];
+  }
+  // fork: the other streams start after whatever the caller enqueued on `s` (uploads of x0, xs, us ...)
+  if (L > 1) {
+    cudaError_t e = cudaEventRecord(p->fork_event, s);
+    for (int k = 1; k < L && e == cudaSuccess; ++k) e = cudaStreamWaitEvent(ls[k], p->fork_event, 0);
     if (e != cudaSuccess) return cuda_fail(e);
   }
   int launches = 0, it = 0;
   const int poll = opts->poll_every > 0 ? opts->poll_every : 1;
-  if (!p->poll_event[0]) {
-    for (int k = 0; k < 2; ++k) {
-      cudaError_t e = cudaEventCreateWithFlags(&p->poll_event[k], cudaEventDisableTiming);
-      if (e != cudaSuccess) return cuda_fail(e);
-    }
+  for (int k = 0; k < L; ++k) {
+    if (launch_init(la[k], ls[k])) return cuda_fail(cudaGetLastError());
+    ++launches;
   }
-  if (launch_init(a, s)) return cuda_fail(cudaGetLastError());
-  ++launches;
   // Pipelined polling: the "OCPs still running" word of poll k is read back asynchronously and only
   // waited for after the iterations up to poll k + 1 have been enqueued, so the GPU never idles on the
-  // host round trip.  A batch that finished costs at most `poll` extra iterations of empty kernels.
-  int pending = -1;  // slot of the poll issued but not yet consumed
-  int n_polls = 0;
-  bool done = false;
-  for (it = 0; it < opts->maxiter && !done; ++it) {
-    a.iter = it;
-    if (p->fn.calcdiff(p->dev, a, s) || p->fn.backward(p->dev, a, s) || p->fn.rollout(p->dev, a, s) ||
-        launch_accept(a, s))
-      return cuda_fail(cudaGetLastError());
-    launches += 3 + p->fn.rollout_launches;  // K1, K2, K3 (rollout phases + trial-cost passes), K4
-    if ((it + 1) % poll == 0 && it + 1 < opts->maxiter) {
-      const int slot = n_polls & 1;
-      if (pending >= 0) {  // consume the previous poll before its slot is reused
-        cudaError_t e = cudaEventSynchronize(p->poll_event[pending]);
+  // host round trip.  A sub-batch that finished costs at most `poll` extra iterations of empty kernels.
+  int pending[ASLR_MAX_LANES], n_polls[ASLR_MAX_LANES], last_it[ASLR_MAX_LANES];
+  bool done[ASLR_MAX_LANES];
+  for (int k = 0; k < L; ++k) pending[k] = -1, n_polls[k] = 0, done[k] = false, last_it[k] = 0;
+  bool all_done = false;
+  for (it = 0; it < opts->maxiter && !all_done; ++it) {
+    all_done = true;
+    for (int k = 0; k < L; ++k) {
+      if (done[k]) continue;
+      SolverArgs& ak = la[k];
+      cudaStream_t sk = ls[k];
+      ak.iter = it;
+      if (p->fn.calcdiff(p->dev, ak, sk) || p->fn.backward(p->dev, ak, sk) || p->fn.rollout(p->dev, ak, sk) ||
+          launch_accept(ak, sk))
+        return cuda_fail(cudaGetLastError());
+      launches += 3 + p->fn.rollout_launches;  // K1, K2, K3 (rollout phases + trial-cost passes), K4
+      last_it[k] = it + 1;
+      if ((it + 1) % poll == 0 && it + 1 < opts->maxiter) {
+        const int slot = n_polls[k] & 1;
+        if (pending[k] >= 0) {  // consume the previous poll before its slot is reused
+          cudaError_t e = cudaEventSynchronize(p->poll_event[2 * k + pending[k]]);
+          if (e != cudaSuccess) return cuda_fail(e);
+          if (p->pinned_counter[2 * k + pending[k]] <= 0) done[k] = true;
+        }
+        cudaError_t e = cudaMemcpyAsync(p->pinned_counter + 2 * k + slot, ak.buf.counters, sizeof(int),
+                                        cudaMemcpyDeviceToHost, sk);
+        if (e == cudaSuccess) e = cudaEventRecord(p->poll_event[2 * k + slot], sk);
         if (e != cudaSuccess) return cuda_fail(e);
-        if (p->pinned_counter[pending] <= 0) done = true;
+        pending[k] = slot;
+        ++n_polls[k];
       }
-      cudaError_t e = cudaMemcpyAsync(p->pinned_counter + slot, buf->counters, sizeof(int), cudaMemcpyDeviceToHost, s);
-      if (e == cudaSuccess) e = cudaEventRecord(p->poll_event[slot], s);
-      if (e != cudaSuccess) return cuda_fail(e);
-      pending = slot;
-      ++n_polls;
+      if (!done[k]) all_done = false;
     }
   }
   // adopt the candidates accepted in the last launched iteration (setCandidate)
-  a.iter = it;
-  if (p->fn.calcdiff(p->dev, a, s) || launch_accept(a, s)) return cuda_fail(cudaGetLastError());
-  launches += 2;
-  cudaError_t e = cudaMemcpyAsync(p->pinned_counter, buf->counters, sizeof(int), cudaMemcpyDeviceToHost, s);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  int n_running = 0, its = 0;
+  for (int k = 0; k < L; ++k) {
+    la[k].iter = last_it[k];
+    if (p->fn.calcdiff(p->dev, la[k], ls[k]) || launch_accept(la[k], ls[k])) return cuda_fail(cudaGetLastError());
+    launches += 2;
+    cudaError_t e = cudaMemcpyAsync(p->pinned_counter + 2 * k, la[k].buf.counters, sizeof(int), cudaMemcpyDeviceToHost,
+                                    ls[k]);
+    if (e == cudaSuccess && k > 0) {  // join: the caller's stream continues after every sub-batch
+      e = cudaEventRecord(p->join_event[k], ls[k]);
+      if (e == cudaSuccess) e = cudaStreamWaitEvent(s, p->join_event[k], 0);
+    }
+    if (e != cudaSuccess) return cuda_fail(e);
+    if (last_it[k] > its) its = last_it[k];
+  }
+  cudaError_t e = cudaStreamSynchronize(s);
   if (e != cudaSuccess) return cuda_fail(e);
+  for (int k = 0; k < L; ++k) n_running += p->pinned_counter[2 * k];
   if (result) {
-    result->iterations_launched = it;
-    result->n_running = p->pinned_counter[0];
+    result->iterations_launched = its;
+    result->n_running = n_running;
     result->n_converged = -1;  // counted by the caller from the state array
     result->kernel_launches = launches;
   }

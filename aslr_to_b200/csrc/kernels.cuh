@@ -325,6 +325,24 @@ struct Launchers {
 
 inline int launch_status() { return cudaGetLastError() == cudaSuccess ? 0 : -2; }
 
+// Opt a kernel in to more than 48 KB of dynamic shared memory, once per kernel and device (the attribute
+// sticks; setting it before every launch was a measurable share of the host's enqueue time once aslr_solve
+// started feeding several streams).
+template <class Kernel>
+inline void allow_smem(Kernel k, size_t bytes) {
+  // keyed by the kernel's address (kernels of equal signature share this instantiation) and the device
+  struct Entry { const void* fn; int dev; int bytes; };
+  static Entry seen[64];
+  static int n_seen = 0;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const void* fn = reinterpret_cast<const void*>(k);
+  for (int i = 0; i < n_seen; ++i)
+    if (seen[i].fn == fn && seen[i].dev == dev && seen[i].bytes >= (int)bytes) return;
+  cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  if (n_seen < 64) seen[n_seen++] = Entry{fn, dev, (int)bytes};
+}
+
 template <int N, bool VSA>
 struct Launch {
   static constexpr int NX = 4 * N;
@@ -342,8 +360,7 @@ struct Launch {
     const unsigned blocks = (unsigned)((total + threads - 1) / threads);
     if (diff) {
       if (N <= ASLR_K1_STAGE_MAXN)
-        cudaFuncSetAttribute(knot_kernel<N, NU, VSA, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)stage_bytes(threads));
+        allow_smem(knot_kernel<N, NU, VSA, true>, stage_bytes(threads));
       knot_kernel<N, NU, VSA, true><<<blocks, threads, stage_bytes(threads), s>>>(P, a);
     }
     else
@@ -355,8 +372,7 @@ struct Launch {
     const long total = (long)a.B * (a.T + 1);
     const int threads = 128;
     if (N <= ASLR_K1_STAGE_MAXN)
-      cudaFuncSetAttribute(solver_calcdiff_kernel<N, NU, VSA>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           (int)stage_bytes(threads));
+      allow_smem(solver_calcdiff_kernel<N, NU, VSA>, stage_bytes(threads));
     solver_calcdiff_kernel<N, NU, VSA>
         <<<(unsigned)((total + threads - 1) / threads), threads, stage_bytes(threads), s>>>(P, a);
     return launch_status();
@@ -368,7 +384,7 @@ struct Launch {
       constexpr int GS = ASLR_ROLLC_GS, TRIALS = ASLR_ROLLC_TRIALS;
       constexpr size_t bytes = sizeof(double) * (ModelConst<N>::SIZE + (size_t)TRIALS * RollSmem<N, NU>::SIZE);
       auto k = rollout_coop_kernel<N, NU, VSA, GS, TRIALS>;
-      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+      allow_smem(k, bytes);
       k<<<(unsigned)((total + TRIALS - 1) / TRIALS), GS * TRIALS, bytes, s>>>(P, a, -1);
       if (launch_status()) return -2;
       trial_cost_kernel<N, NU, VSA><<<(unsigned)(((long)a.B * 32 + 127) / 128), 128, 0, s>>>(P, a, 0);
@@ -398,30 +414,30 @@ struct Launch {
       constexpr int GROUPS = ASLR_BWD_COLS_GROUPS;
       constexpr size_t slice = sizeof(double) * ColsSmem<NX, NU>::SIZE;
       auto k = backward_cols_kernel<NX, NU, GROUPS>;
-      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(slice * GROUPS));
+      allow_smem(k, slice * GROUPS);
       k<<<(a.B + GROUPS - 1) / GROUPS, NX * GROUPS, slice * GROUPS, s>>>(a, lim);
     } else if constexpr (NX > 16 && NX <= 32 && NU <= 8 && ASLR_BWD_ROWS) {
       // (the box QP of SolverBoxDDP stays with the CTA-per-OCP sweep)
       if (!(a.opts.kind == ASLR_SOLVER_BOXDDP && P.has_limits)) {
         constexpr size_t bytes = sizeof(double) * RowsSmem<NX, NU>::SIZE;
         auto k = backward_rows_kernel<NX, NU>;
-        cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        allow_smem(k, bytes);
         k<<<a.B, 32, bytes, s>>>(a);
         return launch_status();
       }
       constexpr int THREADS = ASLR_BWD_CTA_THREADS;
       auto k = backward_cta_kernel<NX, NU, THREADS>;
-      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)per);
+      allow_smem(k, per);
       k<<<a.B, THREADS, per, s>>>(a, lim);
     } else if constexpr (NX <= 12) {
       constexpr int GS = ASLR_BWD_GS, GROUPS = 128 / GS;
       auto k = backward_warp_kernel<NX, NU, GS, GROUPS>;
-      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(per * GROUPS));
+      allow_smem(k, per * GROUPS);
       k<<<(a.B + GROUPS - 1) / GROUPS, GS * GROUPS, per * GROUPS, s>>>(a, lim);
     } else {
       constexpr int THREADS = ASLR_BWD_CTA_THREADS;
       auto k = backward_cta_kernel<NX, NU, THREADS>;
-      cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)per);
+      allow_smem(k, per);
       k<<<a.B, THREADS, per, s>>>(a, lim);
     }
     return launch_status();

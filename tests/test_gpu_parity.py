@@ -220,6 +220,23 @@ def test_ragged_batch_sizes_match_the_host_build(BT, hostmath, B, T):
     assert rel_err(res["states"]["cost"], ref["states"]["cost"]) < 1e-9
 
 
+def test_sub_batch_pipeline_is_bit_identical_to_one_stream(BT, monkeypatch):
+    """aslr_solve cuts large batches into sub-batches on their own streams (api.cu: sub_batch).  OCPs are
+    independent, so the cut must not change a single bit of any output: 37 OCPs in 3 ragged sub-batches
+    against the single-stream sequence."""
+    w = W.sea_batch(37, seed=7)
+    w["T"], w["maxiter"] = 20, 12
+    monkeypatch.setenv("ASLR_SOLVE_LANES", "1")
+    one = gpu_solve(BT, w, T=20)
+    monkeypatch.setenv("ASLR_SOLVE_LANES", "3")
+    monkeypatch.setenv("ASLR_LANE_MIN_OCPS", "1")
+    cut = gpu_solve(BT, w, T=20)
+    for k in ("xs", "us", "Kgain", "kff", "Vx", "log"):
+        assert np.array_equal(np.asarray(one[k]), np.asarray(cut[k])), k
+    for k in ("iter", "status", "cost", "stop", "xreg", "steplength"):
+        assert np.array_equal(one["states"][k], cut["states"][k]), k
+
+
 def test_empty_batch_is_a_no_op(BT):
     w = W.two_dof_sea()
     prob = BT.BatchedShootingProblem(W.to_desc(w), np.zeros((1, 8)), 4)
