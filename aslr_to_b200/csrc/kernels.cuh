@@ -202,7 +202,13 @@ __global__ void __launch_bounds__((N <= 2) ? ASLR_ROLL_THREADS : 64, (N <= 2) ? 
   const int b = (g < a.B) ? (int)g : (int)((g - a.B) / (ASLR_NUM_ALPHAS - 1));
   const int ai = (g < a.B) ? 0 : 1 + (int)((g - a.B) % (ASLR_NUM_ALPHAS - 1));
   if (!rollout_wanted(a, b, ai, phase)) return;
-  rollout_body<N, NU, VSA>(P, a, b, ai);
+  typedef RollStage<4 * N, NU> RS;
+  if constexpr (RS::ENABLED && ASLR_ROLL_THREADS == RS::THREADS) {
+    __shared__ __align__(16) double stage[RS::CTA_DOUBLES];
+    rollout_body<N, NU, VSA>(P, a, b, ai, stage + threadIdx.x * RS::ROW);
+  } else {
+    rollout_body<N, NU, VSA>(P, a, b, ai);
+  }
 }
 
 // K3 for the larger models: GS lanes per trial, per-knot state in shared memory (rollout_coop.cuh)

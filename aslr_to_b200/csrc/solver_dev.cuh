@@ -244,8 +244,39 @@ ASLR_HD void quasi_static_body(const DevProblem<N>& P, const double* x, const do
 // K3: one trial rollout = SolverDDP/FDDP/BoxDDP::forwardPass(alpha) (Appendix A.4) plus the
 // trial-dependent part of FDDP's expectedImprovement.  One thread per (OCP, alpha).
 // ---------------------------------------------------------------------------------------------
+#ifndef ASLR_ROLL_PIPE_MAX
+#define ASLR_ROLL_PIPE_MAX 16  // largest nu * nx whose rollout stages the next step's loads in shared memory
+#endif
+// One thread's staging row of the rollout: [K (nu x nx) | xs (nx) | us (nu) | k (nu)] + 2 doubles of padding, which
+// makes the row stride 240 bytes at (8, 2): the 16-byte accesses of a quarter warp then fall into eight
+// different bank groups.  Two buffers per thread (BUF apart), THREADS rows per buffer.
+template <int NX, int NU>
+struct RollStage {
+  static constexpr bool ENABLED = (NU * NX <= ASLR_ROLL_PIPE_MAX) && (NU % 2 == 0) && (NX % 2 == 0);
+  static constexpr int K = 0, XS = K + NU * NX, US = XS + NX, KF = US + NU, ROW = KF + NU + 2;
+  static constexpr int THREADS = 32;
+  static constexpr int BUF = ROW * THREADS;
+  static constexpr int CTA_DOUBLES = 2 * BUF;
+#if defined(__CUDACC__)
+  static __device__ __forceinline__ void cp16(double* dst, const double* src) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src) : "memory");
+  }
+  static __device__ __forceinline__ void issue(double* row, const double* Kg, const double* xs, const double* us,
+                                               const double* kf) {
+#pragma unroll
+    for (int i = 0; i < NU * NX; i += 2) cp16(row + K + i, Kg + i);
+#pragma unroll
+    for (int i = 0; i < NX; i += 2) cp16(row + XS + i, xs + i);
+#pragma unroll
+    for (int i = 0; i < NU; i += 2) cp16(row + US + i, us + i), cp16(row + KF + i, kf + i);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  static __device__ __forceinline__ void wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+#endif
+};
 template <int N, int NU, bool VSA>
-ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, int ai) {
+ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, int ai, double* stage = nullptr) {
   constexpr int NX = 4 * N;
   const AslrOcpState& s = a.buf.state[b];
   if (s.status != ASLR_OCP_RUNNING) return;
@@ -273,6 +304,18 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
   for (int i = 0; i < NX; ++i) x[i] = a.x0[(size_t)b * NX + i];
   double cost_try = 0.0, dv = 0.0;
   bool ok = true;
+  // Staged loads (CUDA kernel, small models): the gains, candidate state and controls of step t + 1 are copied
+  // with cp.async into this thread's private shared-memory row (RollStage) while the dynamics of step t run,
+  // so the feedback law at the top of a step reads shared memory instead of waiting for L2.  The sample
+  // profile of the latency floor put 21 % of the chain at the first uses of these loads (the L1 prefetch hint
+  // did not shorten them); holding them in registers instead spilled 200 bytes even at 254 registers.
+#if defined(__CUDA_ARCH__)
+  const bool PIPE = RollStage<NX, NU>::ENABLED && stage != nullptr;
+  if (PIPE && T > 0) RollStage<NX, NU>::issue(stage, Kg, xs, us, kf);
+#else
+  const bool PIPE = false;
+  (void)stage;
+#endif
   for (int t = 0; t < T; ++t) {
 #if defined(__CUDA_ARCH__)
     if (t + 1 < T) {  // pull the next step's gains / candidate into L1 while this step's dynamics run
@@ -292,12 +335,26 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
     // 16-byte loads / stores: each thread owns 64-byte rows 6.4 KB apart, so every 8-byte access is its own
     // sector transaction; pairing them halves the LSU work that the dependent loads queue behind
     double dx[NX], fsv[NX], xsv[NX], wvv[NX], Kv[NU * NX], usv[NU], kfv[NU];
-    ld_row<NX>(xsv, xs + (size_t)t * NX);
+    if (PIPE) {
+#if defined(__CUDA_ARCH__)
+      double* row = stage + (t & 1) * RollStage<NX, NU>::BUF;
+      RollStage<NX, NU>::wait();
+      ld_row<NU * NX>(Kv, row + RollStage<NX, NU>::K);
+      ld_row<NX>(xsv, row + RollStage<NX, NU>::XS);
+      ld_row<NU>(usv, row + RollStage<NX, NU>::US);
+      ld_row<NU>(kfv, row + RollStage<NX, NU>::KF);
+      if (t + 1 < T)
+        RollStage<NX, NU>::issue(stage + ((t + 1) & 1) * RollStage<NX, NU>::BUF, Kg + (size_t)(t + 1) * NU * NX,
+                                 xs + (size_t)(t + 1) * NX, us + (size_t)(t + 1) * NU, kf + (size_t)(t + 1) * NU);
+#endif
+    } else {
+      ld_row<NX>(xsv, xs + (size_t)t * NX);
+      ld_row<NU * NX>(Kv, Kg + (size_t)t * NU * NX);
+      ld_row<NU>(usv, us + (size_t)t * NU);
+      ld_row<NU>(kfv, kf + (size_t)t * NU);
+    }
     if (gaps) ld_row<NX>(fsv, fs + (size_t)t * NX);
     if (need_dv) ld_row<NX>(wvv, wv + (size_t)t * NX);
-    ld_row<NU * NX>(Kv, Kg + (size_t)t * NU * NX);
-    ld_row<NU>(usv, us + (size_t)t * NU);
-    ld_row<NU>(kfv, kf + (size_t)t * NU);
 #pragma unroll
     for (int i = 0; i < NX; ++i) {
       if (gaps) x[i] += fsv[i] * (alpha - 1.0);
