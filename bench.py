@@ -494,6 +494,13 @@ def main():
     ap.add_argument("--chain7-ocps", type=int, default=1024)
     ap.add_argument("--solver", default="fddp", choices=["fddp", "ddp"], help="sea4096 workload: SolverFDDP (headline) or SolverDDP")
     args = ap.parse_args()
+    # stdout carries exactly one JSON line.  Native libraries write banners to file descriptor 1 (NCCL prints its
+    # version there whatever NCCL_DEBUG says on this pool): point fd 1 at stderr and keep Python's stdout on a
+    # duplicate of the real one.
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w", buffering=1)
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
     if args.kernels:
         run_kernel_times(args)
     elif args.workload == "chain7_mpc":
