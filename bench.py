@@ -332,10 +332,10 @@ def run_ours(args):
               "share": dict(zip(STAGES, [round(float(v / stage_ms.sum()), 3) for v in stage_ms])),
               "full_batch_us": dict(zip(STAGES, [float(v) for v in rows[1]])),
               "floor_us": dict(zip(STAGES, [float(v) for v in rows[-1]])),
-              "fp64_pipe_frac_ncu": {"calcdiff": 0.26, "backward": 0.21, "rollout": 0.18},
+              "fp64_pipe_frac_ncu": {"calcdiff": 0.26, "backward": 0.21, "rollout": 0.22},
               "note": "stepwise ABI with one event pair and one sync per stage, after the timed region; full_batch = "
                       "iteration 1, floor = last iteration (stragglers only); FP64-pipe utilisation of each kernel at "
-                      "full batch from profiles/r01e_ncu_full.md (rollout: the alpha = 1 phase of a mid-solve iteration; measured FP64 peak 34.2 TFLOP/s)"}
+                      "full batch from profiles/r01e_ncu_full.md (rollout: the alpha = 1 phase of a mid-solve iteration, profiles/r01g_ncu_full_rollout.md; measured FP64 peak 34.2 TFLOP/s)"}
 
     if rank == 0:
         line = {
