@@ -237,6 +237,25 @@ def test_sub_batch_pipeline_is_bit_identical_to_one_stream(BT, monkeypatch):
         assert np.array_equal(one["states"][k], cut["states"][k]), k
 
 
+def test_retries_inside_a_shared_warp_do_not_leak_between_ocps(BT):
+    """The nx = 8 backward kernel runs four OCPs per warp in lockstep; an OCP whose sweep fails (Cholesky of
+    Quu) repeats it with more regularisation while its neighbours ride along as ghosts.  Five double-pendulum
+    OCPs (the example needs ~25 such retries) from different initial angles, solved together and one by one,
+    must give bit-identical outcomes."""
+    w = W.double_pendulum()
+    x0 = np.tile(np.atleast_2d(np.asarray(w["x0"], float)), (5, 1))
+    x0[:, 0] += np.array([0.0, -0.4, 0.3, -1.1, 0.7])
+    x0[:, 2] = x0[:, 0]
+    w = dict(w, x0=x0, maxiter=30)
+    together = gpu_solve(BT, w)
+    assert together["states"]["n_backward_retries"].sum() > 0
+    for b in range(5):
+        alone = gpu_solve(BT, w, ocps=[b])
+        for k in ("iter", "status", "cost", "stop", "xreg", "steplength", "n_backward_retries"):
+            assert alone["states"][k][0] == together["states"][k][b], (b, k)
+        assert np.array_equal(alone["xs"][0], together["xs"][b]) and np.array_equal(alone["us"][0], together["us"][b])
+
+
 def test_empty_batch_is_a_no_op(BT):
     w = W.two_dof_sea()
     prob = BT.BatchedShootingProblem(W.to_desc(w), np.zeros((1, 8)), 4)
