@@ -13,7 +13,8 @@ MAX_COST_TERMS = 6
 NUM_ALPHAS = 10
 LOG_FIELDS = 8
 
-COST_NONE, COST_FRAME_PLACEMENT, COST_STATE, COST_CONTROL, COST_STIFFNESS, COST_DOUBLE_PENDULUM = range(6)
+(COST_NONE, COST_FRAME_PLACEMENT, COST_STATE, COST_CONTROL, COST_STIFFNESS, COST_DOUBLE_PENDULUM,
+ COST_RESIDUAL_DOUBLE_PENDULUM) = range(7)
 DYN_SEA, DYN_VSA = 0, 1
 SOLVER_DDP, SOLVER_FDDP, SOLVER_BOXDDP = 0, 1, 2
 OCP_RUNNING, OCP_CONVERGED, OCP_MAXITER, OCP_REG_MAX = 0, 1, 2, 3
@@ -77,7 +78,7 @@ class OcpState(C.Structure):
     _fields_ = [(k, C.c_double) for k in ("cost", "cost_try", "stop", "xreg", "steplength", "dV", "dVexp", "d1", "d2",
                                           "dg", "dq", "ffeas")] + \
                [(k, C.c_int32) for k in ("iter", "status", "is_feasible", "was_feasible", "recalc", "accepted",
-                                         "src_slot", "n_backward_retries", "full_steps", "reserved0")]
+                                         "src_slot", "n_backward_retries", "full_steps", "n_logged")]
 
 
 OCP_STATE_DOUBLES = C.sizeof(OcpState) // 8
@@ -93,6 +94,13 @@ class SolverBuffers(C.Structure):
 class SolveResult(C.Structure):
     _fields_ = [("iterations_launched", C.c_int32), ("n_converged", C.c_int32), ("n_running", C.c_int32),
                 ("kernel_launches", C.c_int32)]
+
+
+class HostSolveIO(C.Structure):
+    """AslrHostSolveIO: host pointers of aslr_solve_host."""
+    _fields_ = [("B", C.c_int32), ("T", C.c_int32)] + \
+               [(k, C.c_void_p) for k in ("x0", "K_ocp", "mref_ocp", "xs_init", "us_init", "xs", "us", "state", "Kgain",
+                                          "kff", "log")]
 
 
 def record_doubles(nx, nu):
@@ -126,6 +134,7 @@ _PROTOS = {
                                    C.c_int32, C.c_void_p]),
     "aslr_solve": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(SolverOpts), C.POINTER(SolverBuffers),
                              C.POINTER(SolveResult), C.c_void_p]),
+    "aslr_solve_host": (C.c_int, [C.c_void_p, C.POINTER(HostSolveIO), C.POINTER(SolverOpts), C.POINTER(SolveResult)]),
 }
 
 EXPORTED_SYMBOLS = tuple(sorted(_PROTOS))

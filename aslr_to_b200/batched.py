@@ -44,7 +44,7 @@ def decode_states(state_array):
         out[k] = raw[:, i].copy()
     ints = raw[:, len(names_d):].copy().view(np.int32).reshape(B, -1)
     for i, k in enumerate(("iter", "status", "is_feasible", "was_feasible", "recalc", "accepted", "src_slot",
-                           "n_backward_retries", "full_steps")):
+                           "n_backward_retries", "full_steps", "n_logged")):
         out[k] = ints[:, i].copy()
     return out
 
@@ -80,11 +80,18 @@ class BatchedShootingProblem(object):
         self.lib = A.load_library()
         self.desc = desc
         self.handle = C.c_void_p()
-        A.check(self.lib.aslr_problem_create(C.byref(desc), C.byref(self.handle)))
+        # the handle belongs to the device that is current when it is created (include/aslr_b200.h)
+        dev_index = torch.cuda.current_device() if device is None else (torch.device(device).index
+                                                                         if torch.device(device).index is not None
+                                                                         else torch.cuda.current_device())
+        with torch.cuda.device(dev_index):
+            A.check(self.lib.aslr_problem_create(C.byref(desc), C.byref(self.handle)))
         n, nx, nu, rec = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
         A.check(self.lib.aslr_problem_dims(self.handle, C.byref(n), C.byref(nx), C.byref(nu), C.byref(rec)))
         self.n, self.nx, self.nu, self.rec = n.value, nx.value, nu.value, rec.value
         self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
         self.T = int(T)
         self.x0 = self._dev(x0, (-1, self.nx))
         self.B = self.x0.shape[0]
@@ -109,6 +116,11 @@ class BatchedShootingProblem(object):
 
     def _stream(self):
         return C.c_void_p(_torch().cuda.current_stream(self.device).cuda_stream)
+
+    def on_device(self):
+        """Context manager that makes this problem's device current (allocations, streams and every ABI call of a
+        handle happen on the handle's device, whatever the caller's current device is)."""
+        return _torch().cuda.device(self.device)
 
     def _knots(self, fn, xs, us, want):
         torch = _torch()
@@ -222,3 +234,66 @@ class BatchedSolver(object):
         """(B, maxiter, LOG_FIELDS): cost, stop, xreg, steplength, dV, dVexp, ffeas, is_feasible per iteration."""
         B, m = self.problem.B, self.opts.maxiter
         return self.t["log"].reshape(-1)[:B * m * A.LOG_FIELDS].reshape(B, m, A.LOG_FIELDS).cpu().numpy()
+
+
+def solve_host(problem_desc, x0, T, kind=A.SOLVER_FDDP, xs=None, us=None, maxiter=100, th_stop=None, K_ocp=None,
+               mref_ocp=None, is_feasible=False, reg_init=None, want_gains=False, want_log=False, out=None,
+               handle=None, lib=None):
+    """solver.solve(xs, us, maxiter) for a batch of OCPs held in HOST memory (numpy arrays or pinned torch tensors),
+    through aslr_solve_host: the library owns the device workspace and does every copy itself.  Returns a dict of
+    host arrays (xs, us, states, optionally Kgain / kff / log) plus the AslrSolveResult.  `out`: optional dict of
+    preallocated host arrays (e.g. pinned) to receive xs / us / state; `handle`: reuse an AslrProblem handle
+    (keeps the device workspace across calls)."""
+    lib = lib or A.load_library()
+    own = handle is None
+    if own:
+        handle = C.c_void_p()
+        A.check(lib.aslr_problem_create(C.byref(problem_desc), C.byref(handle)))
+    try:
+        n = problem_desc.robot.n
+        nx, nu = 4 * n, problem_desc.dyn.nu
+
+        def host(a, shape):
+            if a is None:
+                return None, None
+            if hasattr(a, "data_ptr"):  # torch CPU tensor (pinned or not)
+                assert a.dtype.itemsize == 8 and a.is_contiguous() and tuple(a.shape) == tuple(shape)
+                return a, a.data_ptr()
+            arr = np.ascontiguousarray(a, dtype=np.float64).reshape(shape)
+            return arr, arr.ctypes.data
+
+        x0a, x0p = host(x0 if hasattr(x0, "data_ptr") else np.atleast_2d(np.asarray(x0, float)),
+                        (len(x0) if np.ndim(x0) == 2 else 1, nx))
+        B = x0a.shape[0]
+        keep = [x0a]
+        io = A.HostSolveIO()
+        io.B, io.T, io.x0 = B, int(T), x0p
+        for name, a, shape in (("K_ocp", K_ocp, (B, n * n)), ("mref_ocp", mref_ocp, (B, 12)),
+                               ("xs_init", xs, (B, T + 1, nx)), ("us_init", us, (B, T, nu))):
+            arr, ptr = host(a, shape)
+            keep.append(arr)
+            setattr(io, name, ptr)
+        out = {} if out is None else out
+        res = {}
+        wants = [("xs", (B, T + 1, nx)), ("us", (B, T, nu)), ("state", (B, A.OCP_STATE_DOUBLES))]
+        if want_gains:
+            wants += [("Kgain", (B, T, nu, nx)), ("kff", (B, T, nu))]
+        if want_log:
+            wants += [("log", (B, max(int(maxiter), 1), A.LOG_FIELDS))]
+        for name, shape in wants:
+            arr = out.get(name)
+            if arr is None:
+                arr = np.zeros(shape)
+            a2, ptr = host(arr, shape)
+            res[name] = a2
+            setattr(io, name, ptr)
+        opts = make_opts(kind, maxiter, th_stop, is_feasible, reg_init, 1, lib)
+        result = A.SolveResult()
+        A.check(lib.aslr_solve_host(handle, C.byref(io), C.byref(opts), C.byref(result)))
+        st = res["state"]
+        res["states"] = decode_states(st.numpy() if hasattr(st, "numpy") else st)
+        res["result"] = result
+        return res
+    finally:
+        if own:
+            lib.aslr_problem_destroy(handle)

@@ -9,7 +9,8 @@ from .. import desc as D
 from ..batched import BatchedShootingProblem
 
 _KIND = {"placement": A.COST_FRAME_PLACEMENT, "state": A.COST_STATE, "control": A.COST_CONTROL,
-         "stiffness": A.COST_STIFFNESS, "pendulum": A.COST_DOUBLE_PENDULUM}
+         "stiffness": A.COST_STIFFNESS, "pendulum": A.COST_DOUBLE_PENDULUM,
+         "pendulum_residual": A.COST_RESIDUAL_DOUBLE_PENDULUM}
 
 
 def term(kind, weight, ref=None, act=None, frame=None):

@@ -127,6 +127,17 @@ class ResidualModelFramePlacementASR(object):
         self.q_dependent, self.v_dependent, self.u_dependent = True, False, False
 
 
+class ResidualModelDoublePendulum(object):
+    """residual_acrobot.py:5-29: r = [s1, s2, 1 + c1, 1 - c2, v1, v2] (q- and v-dependent, not u-dependent);
+    used through crocoddyl.CostModelResidual(state, activation, residual)."""
+
+    def __init__(self, state, nu):
+        if state.pinocchio.nv != 2:
+            raise ValueError("ResidualModelDoublePendulum indexes x[4], x[5] as the link velocities: 2 link DOF only")
+        self.state, self.nu, self.nr = state, int(nu), 6
+        self.q_dependent, self.v_dependent, self.u_dependent = True, True, False
+
+
 class CostModelStiffness(object):
     """stiffness_cost.py:6-20: cost = sum(lamda (sigma - Kref)), linear in the stiffness controls."""
 

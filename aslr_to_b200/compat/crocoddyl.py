@@ -75,6 +75,8 @@ class CostModelResidual(object):
             M = r.reference
             ref = np.concatenate([np.asarray(M.rotation, float).reshape(9), np.asarray(M.translation, float).reshape(3)])
             return E.term("placement", weight, ref=ref, act=w, frame=r.state.pinocchio._frame_desc(r.id))
+        if type(r).__name__ == "ResidualModelDoublePendulum":
+            return E.term("pendulum_residual", weight, act=w)
         raise NotImplementedError("residual %s has no CUDA implementation" % type(r).__name__)
 
 
@@ -277,8 +279,9 @@ class _Solver(object):
         self.Vx, self.Vxx = list(g("Vx")), list(g("Vxx"))
         self.Qu, self.Quu = list(g("Qu")), list(g("Quu"))
         log = bs.logs()[0]
-        n_it = int(st["iter"]) if st["status"] == A.OCP_MAXITER else int(st["iter"]) + 1
-        n_it = min(n_it, int(maxiter))
+        # exactly the iterations whose callbacks crocoddyl runs: an iteration that ends at reg_max (in the
+        # backward pass or after the line search) returns before the callbacks and has no log row
+        n_it = min(int(st["n_logged"]), int(maxiter))
         for it in range(n_it):  # replay the per-iteration callbacks from the device log
             c, stop, xreg, step, dV, dVexp, ffeas, feas = log[it]
             self.cost, self.stop, self.x_reg, self.u_reg, self.stepLength = c, stop, xreg, xreg, step

@@ -7,6 +7,7 @@ import types
 from . import pinocchio
 
 _ALIASES = {"asr_twodof": "asr_twodof", "double_pendulum": "double_pendulum", "chain7": "chain7"}
+_ALIASES.update(("chain%d" % n, "chain%d" % n) for n in range(1, 7))
 
 
 def load(name):

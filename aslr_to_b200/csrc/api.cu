@@ -70,16 +70,52 @@ struct AslrProblem {
   AslrProblemDesc desc;
   int n, nx, nu;
   bool vsa;
+  int device;  // the CUDA device that was current at aslr_problem_create: every entry point runs on it
   Launchers fn;
   // DevProblem<N> for the instantiated N (largest is N = 7)
   alignas(16) unsigned char dev[sizeof(DevProblem<ASLR_MAX_DOF>)];
   // aslr_solve: host-pinned mirrors of the "OCPs still running" words (two poll slots per sub-batch) and the
-  // streams / events of the sub-batch pipeline
+  // streams / events of the sub-batch pipeline.  `pipeline_ready` is set only after every one of them exists.
+  bool pipeline_ready;
+  int lanes, lane_min_ocps;  // ASLR_SOLVE_LANES / ASLR_LANE_MIN_OCPS, read from the environment once at create
   int* pinned_counter;
   cudaEvent_t poll_event[2 * ASLR_MAX_LANES];
   cudaStream_t lane_stream[ASLR_MAX_LANES];  // [0] unused: sub-batch 0 runs on the caller's stream
   cudaEvent_t fork_event, join_event[ASLR_MAX_LANES];
+  // aslr_solve_host: device workspace and pinned staging owned by the handle (grow-only)
+  struct HostWs {
+    cudaStream_t stream;
+    int B, T, maxiter;          // capacity the device arrays were sized for
+    double* dev_block;          // one allocation holding every array of AslrSolverBuffers + x0 / K / mref
+    size_t dev_doubles;
+    double* pin_in;             // pinned staging for pageable inputs
+    double* pin_out;            // pinned staging for pageable outputs
+    size_t pin_in_doubles, pin_out_doubles;
+  } ws;
 };
+
+namespace {
+// every entry point runs on the handle's device whatever the caller's current device is (a handle
+// used from a thread whose current device differs would launch with foreign streams / pointers)
+struct DeviceGuard {
+  int prev;
+  bool switched, ok;
+  explicit DeviceGuard(int want) : prev(-1), switched(false), ok(true) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+    if (prev != want) {
+      ok = cudaSetDevice(want) == cudaSuccess;
+      switched = ok;
+    }
+  }
+  ~DeviceGuard() {
+    if (switched) cudaSetDevice(prev);
+  }
+};
+int env_int(const char* name, int dflt) {
+  const char* ev = getenv(name);
+  return ev ? atoi(ev) : dflt;
+}
+}  // namespace
 
 extern "C" {
 
@@ -128,10 +164,12 @@ int aslr_problem_create(const AslrProblemDesc* desc, AslrProblem** out) {
     const AslrCostSum& cs = pass ? desc->terminal : desc->running;
     for (int k = 0; k < cs.nterms; ++k) {
       const AslrCostTerm& t = cs.terms[k];
-      if (t.kind < ASLR_COST_FRAME_PLACEMENT || t.kind > ASLR_COST_DOUBLE_PENDULUM) return fail(ASLR_ERR_INVALID, "unknown cost kind%s");
+      if (t.kind < ASLR_COST_FRAME_PLACEMENT || t.kind > ASLR_COST_RESIDUAL_DOUBLE_PENDULUM)
+        return fail(ASLR_ERR_INVALID, "unknown cost kind%s");
       if (t.kind == ASLR_COST_FRAME_PLACEMENT && (t.frame_parent < 0 || t.frame_parent >= n))
         return fail(ASLR_ERR_INVALID, "frame parent joint out of range%s");
-      if (t.kind == ASLR_COST_DOUBLE_PENDULUM && n != 2) return fail(ASLR_ERR_INVALID, "the double-pendulum cost needs n = 2%s");
+      if ((t.kind == ASLR_COST_DOUBLE_PENDULUM || t.kind == ASLR_COST_RESIDUAL_DOUBLE_PENDULUM) && n != 2)
+        return fail(ASLR_ERR_INVALID, "the double-pendulum cost / residual needs n = 2%s");
       if (t.kind == ASLR_COST_STIFFNESS && !vsa) return fail(ASLR_ERR_INVALID, "the stiffness cost needs the VSA model%s");
     }
   }
@@ -142,35 +180,40 @@ int aslr_problem_create(const AslrProblemDesc* desc, AslrProblem** out) {
   p->nx = 4 * n;
   p->nu = desc->dyn.nu;
   p->vsa = vsa;
+  p->device = 0;
+  cudaGetDevice(&p->device);  // stays 0 without a device: every launch then fails loudly (no CPU fallback)
+  p->pipeline_ready = false;
+  p->lanes = env_int("ASLR_SOLVE_LANES", ASLR_SOLVE_LANES);
+  p->lane_min_ocps = env_int("ASLR_LANE_MIN_OCPS", ASLR_LANE_MIN_OCPS);
+  std::memset(&p->ws, 0, sizeof(p->ws));
   p->pinned_counter = nullptr;
   p->fork_event = nullptr;
   for (int k = 0; k < 2 * ASLR_MAX_LANES; ++k) p->poll_event[k] = nullptr;
   for (int k = 0; k < ASLR_MAX_LANES; ++k) p->lane_stream[k] = nullptr, p->join_event[k] = nullptr;
   std::memset(p->dev, 0, sizeof(p->dev));
-  if (n == 2) {
-    fill_dev_problem<2>(*desc, *reinterpret_cast<DevProblem<2>*>(p->dev));
-    p->fn = launchers_n2(vsa);
-  } else if (n == 7) {
-    fill_dev_problem<7>(*desc, *reinterpret_cast<DevProblem<7>*>(p->dev));
-    p->fn = launchers_n7(vsa);
-  } else {
-    delete p;
-    return fail(ASLR_ERR_UNSUPPORTED, "kernels are instantiated for n = 2 and n = 7 link DOF only%s");
+  switch (n) {
+#define ASLR_CASE(N)                                                          \
+  case N:                                                                     \
+    fill_dev_problem<N>(*desc, *reinterpret_cast<DevProblem<N>*>(p->dev));    \
+    p->fn = launchers_n##N(vsa);                                              \
+    break;
+    ASLR_CASE(1) ASLR_CASE(2) ASLR_CASE(3) ASLR_CASE(4) ASLR_CASE(5) ASLR_CASE(6) ASLR_CASE(7)
+#undef ASLR_CASE
+    default:
+      delete p;
+      return fail(ASLR_ERR_UNSUPPORTED, "link DOF must be 1..7 (ASLR_MAX_DOF)%s");
   }
   *out = p;
   return ASLR_OK;
 }
 
+static void host_ws_destroy(AslrProblem* p);
+static void pipeline_destroy(AslrProblem* p);
 int aslr_problem_destroy(AslrProblem* p) {
   if (p) {
-    if (p->pinned_counter) cudaFreeHost(p->pinned_counter);
-    for (int k = 0; k < 2 * ASLR_MAX_LANES; ++k)
-      if (p->poll_event[k]) cudaEventDestroy(p->poll_event[k]);
-    if (p->fork_event) cudaEventDestroy(p->fork_event);
-    for (int k = 0; k < ASLR_MAX_LANES; ++k) {
-      if (p->join_event[k]) cudaEventDestroy(p->join_event[k]);
-      if (p->lane_stream[k]) cudaStreamDestroy(p->lane_stream[k]);
-    }
+    DeviceGuard dg(p->device);
+    pipeline_destroy(p);
+    host_ws_destroy(p);
     delete p;
   }
   return ASLR_OK;
@@ -189,6 +232,8 @@ static int knots(const AslrProblem* p, const AslrBatch* batch, const double* xs,
                  const AslrKnotOut* out, int diff, void* stream) {
   if (!p || !batch || !xs || !out) return fail(ASLR_ERR_INVALID, "null argument%s");
   if (batch->B < 0 || batch->T < 0) return fail(ASLR_ERR_INVALID, "negative batch dimension%s");
+  DeviceGuard dg(p->device);
+  if (!dg.ok) return fail(ASLR_ERR_CUDA, "cannot make the handle's device current%s");
   KnotArgs a;
   a.B = batch->B, a.T = batch->T, a.xs = xs, a.us = us, a.K_ocp = batch->K_ocp, a.mref_ocp = batch->mref_ocp;
   a.out = *out;
@@ -209,6 +254,8 @@ int aslr_quasi_static(const AslrProblem* p, const AslrBatch* batch, const double
                       double tol, void* stream) {
   if (!p || !batch || !xs || !us) return fail(ASLR_ERR_INVALID, "null argument%s");
   if (batch->B < 0 || batch->T < 0 || maxiter < 0) return fail(ASLR_ERR_INVALID, "negative dimension%s");
+  DeviceGuard dg(p->device);
+  if (!dg.ok) return fail(ASLR_ERR_CUDA, "cannot make the handle's device current%s");
   KnotArgs a;
   a.B = batch->B, a.T = batch->T, a.xs = xs, a.us = nullptr, a.K_ocp = batch->K_ocp, a.mref_ocp = batch->mref_ocp;
   a.out = AslrKnotOut{};
@@ -220,6 +267,8 @@ int aslr_shift_warm_start(const AslrProblem* p, const AslrBatch* batch, double* 
                           void* stream) {
   if (!p || !batch || !xs || !us) return fail(ASLR_ERR_INVALID, "null argument%s");
   if (batch->B <= 0 || batch->T <= 0) return fail(ASLR_ERR_INVALID, "B and T must be positive%s");
+  DeviceGuard dg(p->device);
+  if (!dg.ok) return fail(ASLR_ERR_CUDA, "cannot make the handle's device current%s");
   const int total = batch->B * (p->nx + p->nu);
   shift_kernel<<<(total + 127) / 128, 128, 0, (cudaStream_t)stream>>>(batch->B, batch->T, p->nx, p->nu, xs, us, x0_new);
   if (launch_status()) return cuda_fail(cudaGetLastError());
@@ -249,6 +298,8 @@ int aslr_solver_init(const AslrProblem* p, const AslrBatch* batch, const AslrSol
                      const AslrSolverBuffers* buf, void* stream) {
   SolverArgs a;
   if (int rc = make_args(p, batch, opts, buf, 0, &a)) return rc;
+  DeviceGuard dg(p->device);
+  if (!dg.ok) return fail(ASLR_ERR_CUDA, "cannot make the handle's device current%s");
   if (launch_init(a, (cudaStream_t)stream)) return cuda_fail(cudaGetLastError());
   return ASLR_OK;
 }
@@ -256,6 +307,8 @@ int aslr_solver_calc_diff(const AslrProblem* p, const AslrBatch* batch, const As
                           const AslrSolverBuffers* buf, int32_t iter, void* stream) {
   SolverArgs a;
   if (int rc = make_args(p, batch, opts, buf, iter, &a)) return rc;
+  DeviceGuard dg(p->device);
+  if (!dg.ok) return fail(ASLR_ERR_CUDA, "cannot make the handle's device current%s");
   if (p->fn.calcdiff(p->dev, a, (cudaStream_t)stream)) return cuda_fail(cudaGetLastError());
   return ASLR_OK;
 }
@@ -263,6 +316,8 @@ int aslr_backward_pass(const AslrProblem* p, const AslrBatch* batch, const AslrS
                        const AslrSolverBuffers* buf, void* stream) {
   SolverArgs a;
   if (int rc = make_args(p, batch, opts, buf, 0, &a)) return rc;
+  DeviceGuard dg(p->device);
+  if (!dg.ok) return fail(ASLR_ERR_CUDA, "cannot make the handle's device current%s");
   if (p->fn.backward(p->dev, a, (cudaStream_t)stream)) return cuda_fail(cudaGetLastError());
   return ASLR_OK;
 }
@@ -270,6 +325,8 @@ int aslr_forward_pass(const AslrProblem* p, const AslrBatch* batch, const AslrSo
                       const AslrSolverBuffers* buf, void* stream) {
   SolverArgs a;
   if (int rc = make_args(p, batch, opts, buf, 0, &a)) return rc;
+  DeviceGuard dg(p->device);
+  if (!dg.ok) return fail(ASLR_ERR_CUDA, "cannot make the handle's device current%s");
   if (p->fn.rollout(p->dev, a, (cudaStream_t)stream)) return cuda_fail(cudaGetLastError());
   return ASLR_OK;
 }
@@ -277,6 +334,8 @@ int aslr_accept_step(const AslrProblem* p, const AslrBatch* batch, const AslrSol
                      const AslrSolverBuffers* buf, int32_t iter, void* stream) {
   SolverArgs a;
   if (int rc = make_args(p, batch, opts, buf, iter, &a)) return rc;
+  DeviceGuard dg(p->device);
+  if (!dg.ok) return fail(ASLR_ERR_CUDA, "cannot make the handle's device current%s");
   if (launch_accept(a, (cudaStream_t)stream)) return cuda_fail(cudaGetLastError());
   return ASLR_OK;
 }
@@ -312,33 +371,58 @@ static SolverArgs sub_batch(const SolverArgs& a, const AslrProblem* p, int b0, i
 // stage of one sub-batch runs under the throughput-bound stages of the others.  Results do not depend on the
 // cut (no kernel looks across OCPs).  Measured gain is modest (4 %): the chains that now overlap with K1 / K2
 // of other sub-batches share issue slots and the FP64 pipe with them and get slower themselves.
-// ASLR_SOLVE_LANES in the environment overrides the number of sub-batches (1 = the single-stream sequence).
+// ASLR_SOLVE_LANES in the environment (read once, at aslr_problem_create) overrides the number of sub-batches
+// (1 = the single-stream sequence).
+
+// streams, events and the pinned poll words of the pipeline: all or nothing
+static void pipeline_destroy(AslrProblem* p) {
+  if (p->pinned_counter) cudaFreeHost(p->pinned_counter);
+  p->pinned_counter = nullptr;
+  for (int k = 0; k < 2 * ASLR_MAX_LANES; ++k) {
+    if (p->poll_event[k]) cudaEventDestroy(p->poll_event[k]);
+    p->poll_event[k] = nullptr;
+  }
+  if (p->fork_event) cudaEventDestroy(p->fork_event);
+  p->fork_event = nullptr;
+  for (int k = 0; k < ASLR_MAX_LANES; ++k) {
+    if (p->join_event[k]) cudaEventDestroy(p->join_event[k]);
+    if (p->lane_stream[k]) cudaStreamDestroy(p->lane_stream[k]);
+    p->join_event[k] = nullptr, p->lane_stream[k] = nullptr;
+  }
+  p->pipeline_ready = false;
+}
+static int pipeline_create(AslrProblem* p) {
+  if (p->pipeline_ready) return ASLR_OK;
+  cudaError_t e = cudaMallocHost((void**)&p->pinned_counter, 2 * ASLR_MAX_LANES * sizeof(int));
+  for (int k = 0; k < 2 * ASLR_MAX_LANES && e == cudaSuccess; ++k)
+    e = cudaEventCreateWithFlags(&p->poll_event[k], cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->fork_event, cudaEventDisableTiming);
+  for (int k = 1; k < ASLR_MAX_LANES && e == cudaSuccess; ++k) {
+    e = cudaStreamCreateWithFlags(&p->lane_stream[k], cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->join_event[k], cudaEventDisableTiming);
+  }
+  if (e != cudaSuccess) {
+    pipeline_destroy(p);  // a half-built pipeline must not look initialised to the next call
+    return cuda_fail(e);
+  }
+  p->pipeline_ready = true;
+  return ASLR_OK;
+}
+
 int aslr_solve(const AslrProblem* pc, const AslrBatch* batch, const AslrSolverOpts* opts, const AslrSolverBuffers* buf,
                AslrSolveResult* result, void* stream) {
   AslrProblem* p = const_cast<AslrProblem*>(pc);
   SolverArgs a;
   if (int rc = make_args(p, batch, opts, buf, 0, &a)) return rc;
+  DeviceGuard dg(p->device);
+  if (!dg.ok) return fail(ASLR_ERR_CUDA, "cannot make the handle's device current%s");
   cudaStream_t s = (cudaStream_t)stream;
-  int L = ASLR_SOLVE_LANES;
-  if (const char* ev = getenv("ASLR_SOLVE_LANES")) L = atoi(ev);
+  int L = p->lanes;
   if (L > ASLR_MAX_LANES) L = ASLR_MAX_LANES;
-  int min_ocps = ASLR_LANE_MIN_OCPS;
-  if (const char* ev = getenv("ASLR_LANE_MIN_OCPS")) min_ocps = atoi(ev);
-  if (min_ocps < 1) min_ocps = 1;
+  const int min_ocps = p->lane_min_ocps < 1 ? 1 : p->lane_min_ocps;
   while (L > 1 && batch->B / L < min_ocps) --L;
   if (L < 1) L = 1;
-  if (!p->pinned_counter) {
-    cudaError_t e = cudaMallocHost((void**)&p->pinned_counter, 2 * ASLR_MAX_LANES * sizeof(int));
-    if (e != cudaSuccess) return cuda_fail(e);
-    for (int k = 0; k < 2 * ASLR_MAX_LANES && e == cudaSuccess; ++k)
-      e = cudaEventCreateWithFlags(&p->poll_event[k], cudaEventDisableTiming);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->fork_event, cudaEventDisableTiming);
-    for (int k = 1; k < ASLR_MAX_LANES && e == cudaSuccess; ++k) {
-      e = cudaStreamCreateWithFlags(&p->lane_stream[k], cudaStreamNonBlocking);
-      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->join_event[k], cudaEventDisableTiming);
-    }
-    if (e != cudaSuccess) return cuda_fail(e);
-  }
+  if (int rc = pipeline_create(p)) return rc;
   SolverArgs la[ASLR_MAX_LANES];
   cudaStream_t ls[ASLR_MAX_LANES];
   for (int k = 0; k < L; ++k) {
@@ -352,10 +436,18 @@ int aslr_solve(const AslrProblem* pc, const AslrBatch* batch, const AslrSolverOp
     for (int k = 1; k < L && e == cudaSuccess; ++k) e = cudaStreamWaitEvent(ls[k], p->fork_event, 0);
     if (e != cudaSuccess) return cuda_fail(e);
   }
+  // Error exit after the fork: the sub-batch streams may hold kernels and asynchronous copies into the pinned
+  // poll words; wait for all of them so that nothing of this call is still in flight when the caller sees the
+  // error (and the caller's stream is not left un-joined).
+  auto bail = [&](cudaError_t e) {
+    const int rc = cuda_fail(e != cudaSuccess ? e : cudaGetLastError());
+    for (int k = 0; k < L; ++k) cudaStreamSynchronize(ls[k]);
+    return rc;
+  };
   int launches = 0, it = 0;
   const int poll = opts->poll_every > 0 ? opts->poll_every : 1;
   for (int k = 0; k < L; ++k) {
-    if (launch_init(la[k], ls[k])) return cuda_fail(cudaGetLastError());
+    if (launch_init(la[k], ls[k])) return bail(cudaSuccess);
     ++launches;
   }
   // Pipelined polling: the "OCPs still running" word of poll k is read back asynchronously and only
@@ -374,49 +466,199 @@ int aslr_solve(const AslrProblem* pc, const AslrBatch* batch, const AslrSolverOp
       ak.iter = it;
       if (p->fn.calcdiff(p->dev, ak, sk) || p->fn.backward(p->dev, ak, sk) || p->fn.rollout(p->dev, ak, sk) ||
           launch_accept(ak, sk))
-        return cuda_fail(cudaGetLastError());
+        return bail(cudaSuccess);
       launches += 3 + p->fn.rollout_launches;  // K1, K2, K3 (rollout phases + trial-cost passes), K4
       last_it[k] = it + 1;
       if ((it + 1) % poll == 0 && it + 1 < opts->maxiter) {
         const int slot = n_polls[k] & 1;
         if (pending[k] >= 0) {  // consume the previous poll before its slot is reused
           cudaError_t e = cudaEventSynchronize(p->poll_event[2 * k + pending[k]]);
-          if (e != cudaSuccess) return cuda_fail(e);
+          if (e != cudaSuccess) return bail(e);
           if (p->pinned_counter[2 * k + pending[k]] <= 0) done[k] = true;
         }
         cudaError_t e = cudaMemcpyAsync(p->pinned_counter + 2 * k + slot, ak.buf.counters, sizeof(int),
                                         cudaMemcpyDeviceToHost, sk);
         if (e == cudaSuccess) e = cudaEventRecord(p->poll_event[2 * k + slot], sk);
-        if (e != cudaSuccess) return cuda_fail(e);
+        if (e != cudaSuccess) return bail(e);
         pending[k] = slot;
         ++n_polls[k];
       }
       if (!done[k]) all_done = false;
     }
   }
-  // adopt the candidates accepted in the last launched iteration (setCandidate)
+  // adopt the candidates accepted in the last launched iteration (setCandidate).  With maxiter = 0 no iteration
+  // ran: there is no trial to adopt and no log row to write, the OCPs simply stay RUNNING (crocoddyl's
+  // solve(xs, us, 0) returns False without touching the candidate).
   int n_running = 0, its = 0;
   for (int k = 0; k < L; ++k) {
     la[k].iter = last_it[k];
-    if (p->fn.calcdiff(p->dev, la[k], ls[k]) || launch_accept(la[k], ls[k])) return cuda_fail(cudaGetLastError());
-    launches += 2;
+    if (opts->maxiter > 0) {
+      if (p->fn.calcdiff(p->dev, la[k], ls[k]) || launch_accept(la[k], ls[k])) return bail(cudaSuccess);
+      launches += 2;
+    }
     cudaError_t e = cudaMemcpyAsync(p->pinned_counter + 2 * k, la[k].buf.counters, sizeof(int), cudaMemcpyDeviceToHost,
                                     ls[k]);
     if (e == cudaSuccess && k > 0) {  // join: the caller's stream continues after every sub-batch
       e = cudaEventRecord(p->join_event[k], ls[k]);
       if (e == cudaSuccess) e = cudaStreamWaitEvent(s, p->join_event[k], 0);
     }
-    if (e != cudaSuccess) return cuda_fail(e);
+    if (e != cudaSuccess) return bail(e);
     if (last_it[k] > its) its = last_it[k];
   }
   cudaError_t e = cudaStreamSynchronize(s);
-  if (e != cudaSuccess) return cuda_fail(e);
+  if (e != cudaSuccess) return bail(e);
   for (int k = 0; k < L; ++k) n_running += p->pinned_counter[2 * k];
   if (result) {
     result->iterations_launched = its;
     result->n_running = n_running;
     result->n_converged = -1;  // counted by the caller from the state array
     result->kernel_launches = launches;
+  }
+  return ASLR_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// aslr_solve_host: solver.solve(xs, us, maxiter) with HOST buffers on both sides.  The handle owns the device
+// workspace (every array of AslrSolverBuffers + x0 / K / mref, one grow-only allocation), a stream and two
+// pinned staging areas.  A host pointer that is already page-locked (cudaHostAlloc / cudaHostRegister / a
+// pinned torch tensor) is copied straight from / to the caller's memory; pageable memory goes through the
+// pinned staging so that every transfer is a genuine asynchronous DMA.
+// ------------------------------------------------------------------------------------------------
+static void host_ws_destroy(AslrProblem* p) {
+  AslrProblem::HostWs& w = p->ws;
+  if (w.dev_block) cudaFree(w.dev_block);
+  if (w.pin_in) cudaFreeHost(w.pin_in);
+  if (w.pin_out) cudaFreeHost(w.pin_out);
+  if (w.stream) cudaStreamDestroy(w.stream);
+  std::memset(&w, 0, sizeof(w));
+}
+
+static bool host_ptr_is_pinned(const void* q) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, q) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeHost;
+}
+
+int aslr_solve_host(AslrProblem* p, const AslrHostSolveIO* io, const AslrSolverOpts* opts, AslrSolveResult* result) {
+  if (!p || !io || !opts) return fail(ASLR_ERR_INVALID, "null argument%s");
+  if (io->B <= 0 || io->T <= 0) return fail(ASLR_ERR_INVALID, "B and T must be positive%s");
+  if (!io->x0 || !io->xs || !io->us || !io->state) return fail(ASLR_ERR_INVALID, "x0, xs, us and state are required%s");
+  if (opts->maxiter < 0) return fail(ASLR_ERR_INVALID, "negative maxiter%s");
+  DeviceGuard dg(p->device);
+  if (!dg.ok) return fail(ASLR_ERR_CUDA, "cannot make the handle's device current%s");
+  AslrProblem::HostWs& w = p->ws;
+  const size_t B = io->B, T = io->T, nx = p->nx, nu = p->nu, n = p->n, rec = aslr_record_doubles(p->nx, p->nu);
+  const size_t mi = opts->maxiter > 0 ? opts->maxiter : 1;
+  // ---- device workspace: segment sizes in doubles, each rounded up to 32 doubles (256 bytes)
+  enum { XS, US, XNEXT, KCOST, DERIV, FS, KG, KF, VX, VXXFS, QU, QUUK, XTRY, UTRY, TRIAL, LOG, STATE, CNT, X0, KO, MREF, NSEG };
+  size_t sz[NSEG];
+  sz[XS] = B * (T + 1) * nx, sz[US] = B * T * nu, sz[XNEXT] = B * T * nx, sz[KCOST] = B * (T + 1);
+  sz[DERIV] = B * (T + 1) * rec, sz[FS] = B * (T + 1) * nx, sz[KG] = B * T * nu * nx, sz[KF] = B * T * nu;
+  sz[VX] = B * (T + 1) * nx, sz[VXXFS] = B * (T + 1) * nx, sz[QU] = B * T * nu, sz[QUUK] = B * T * nu;
+  sz[XTRY] = B * ASLR_NUM_ALPHAS * (T + 1) * nx, sz[UTRY] = B * ASLR_NUM_ALPHAS * T * nu;
+  sz[TRIAL] = B * ASLR_NUM_ALPHAS * 4, sz[LOG] = io->log ? B * mi * ASLR_LOG_FIELDS : 0;
+  sz[STATE] = B * (sizeof(AslrOcpState) / sizeof(double)), sz[CNT] = 2;
+  sz[X0] = B * nx, sz[KO] = io->K_ocp ? B * n * n : 0, sz[MREF] = io->mref_ocp ? B * 12 : 0;
+  size_t off[NSEG], total = 0;
+  for (int k = 0; k < NSEG; ++k) off[k] = total, total += (sz[k] + 31) & ~(size_t)31;
+  if (!w.stream) {
+    cudaError_t e = cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) return cuda_fail(e);
+  }
+  if (total > w.dev_doubles) {
+    if (w.dev_block) cudaFree(w.dev_block);
+    w.dev_block = nullptr, w.dev_doubles = 0;
+    cudaError_t e = cudaMalloc((void**)&w.dev_block, total * sizeof(double));
+    if (e != cudaSuccess) return cuda_fail(e);
+    w.dev_doubles = total;
+  }
+  double* D = w.dev_block;
+  // ---- pinned staging, sized for the pageable arrays of this call only
+  struct In { const double* src; int seg; } ins[] = {{io->x0, X0}, {io->K_ocp, KO}, {io->mref_ocp, MREF},
+                                                     {io->xs_init, XS}, {io->us_init, US}};
+  struct Out { void* dst; int seg; } outs[] = {{io->xs, XS}, {io->us, US}, {io->state, STATE}, {io->Kgain, KG},
+                                               {io->kff, KF}, {io->log, LOG}};
+  size_t need_in = 0, need_out = 0;
+  bool in_pinned[5], out_pinned[6];
+  for (int k = 0; k < 5; ++k) {
+    in_pinned[k] = ins[k].src && host_ptr_is_pinned(ins[k].src);
+    if (ins[k].src && !in_pinned[k]) need_in += sz[ins[k].seg];
+  }
+  for (int k = 0; k < 6; ++k) {
+    out_pinned[k] = outs[k].dst && host_ptr_is_pinned(outs[k].dst);
+    if (outs[k].dst && !out_pinned[k]) need_out += sz[outs[k].seg];
+  }
+  if (need_in > w.pin_in_doubles) {
+    if (w.pin_in) cudaFreeHost(w.pin_in);
+    w.pin_in = nullptr, w.pin_in_doubles = 0;
+    cudaError_t e = cudaMallocHost((void**)&w.pin_in, need_in * sizeof(double));
+    if (e != cudaSuccess) return cuda_fail(e);
+    w.pin_in_doubles = need_in;
+  }
+  if (need_out > w.pin_out_doubles) {
+    if (w.pin_out) cudaFreeHost(w.pin_out);
+    w.pin_out = nullptr, w.pin_out_doubles = 0;
+    cudaError_t e = cudaMallocHost((void**)&w.pin_out, need_out * sizeof(double));
+    if (e != cudaSuccess) return cuda_fail(e);
+    w.pin_out_doubles = need_out;
+  }
+  cudaStream_t s = w.stream;
+  cudaError_t e = cudaSuccess;
+  // ---- host -> device
+  size_t cur = 0;
+  for (int k = 0; k < 5 && e == cudaSuccess; ++k) {
+    const size_t bytes = sz[ins[k].seg] * sizeof(double);
+    if (!ins[k].src) {
+      // xs_init / us_init absent: setCandidate([], []) = state.zero() / zero controls
+      if (ins[k].seg == XS || ins[k].seg == US) e = cudaMemsetAsync(D + off[ins[k].seg], 0, bytes, s);
+      continue;
+    }
+    const double* src = ins[k].src;
+    if (!in_pinned[k]) {
+      std::memcpy(w.pin_in + cur, src, bytes);
+      src = w.pin_in + cur;
+      cur += sz[ins[k].seg];
+    }
+    e = cudaMemcpyAsync(D + off[ins[k].seg], src, bytes, cudaMemcpyHostToDevice, s);
+  }
+  if (e != cudaSuccess) return cuda_fail(e);
+  // ---- solve on the workspace
+  AslrBatch batch;
+  batch.B = io->B, batch.T = io->T, batch.x0 = D + off[X0];
+  batch.K_ocp = io->K_ocp ? D + off[KO] : nullptr;
+  batch.mref_ocp = io->mref_ocp ? D + off[MREF] : nullptr;
+  AslrSolverBuffers buf;
+  std::memset(&buf, 0, sizeof(buf));
+  buf.xs = D + off[XS], buf.us = D + off[US], buf.xnext = D + off[XNEXT], buf.knot_cost = D + off[KCOST];
+  buf.deriv = D + off[DERIV], buf.fs = D + off[FS], buf.Kgain = D + off[KG], buf.kff = D + off[KF];
+  buf.Vx = D + off[VX], buf.Vxxfs = D + off[VXXFS], buf.Qu = D + off[QU], buf.Quuk = D + off[QUUK];
+  buf.xs_try = D + off[XTRY], buf.us_try = D + off[UTRY], buf.trial = D + off[TRIAL];
+  buf.log = io->log ? D + off[LOG] : nullptr;
+  buf.state = reinterpret_cast<AslrOcpState*>(D + off[STATE]);
+  buf.counters = reinterpret_cast<int32_t*>(D + off[CNT]);
+  if (int rc = aslr_solve(p, &batch, opts, &buf, result, s)) return rc;
+  // ---- device -> host
+  cur = 0;
+  for (int k = 0; k < 6 && e == cudaSuccess; ++k) {
+    if (!outs[k].dst) continue;
+    const size_t bytes = sz[outs[k].seg] * sizeof(double);
+    void* dst = outs[k].dst;
+    if (!out_pinned[k]) {
+      dst = w.pin_out + cur;
+      cur += sz[outs[k].seg];
+    }
+    e = cudaMemcpyAsync(dst, D + off[outs[k].seg], bytes, cudaMemcpyDeviceToHost, s);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  if (e != cudaSuccess) return cuda_fail(e);
+  cur = 0;
+  for (int k = 0; k < 6; ++k) {
+    if (!outs[k].dst || out_pinned[k]) continue;
+    std::memcpy(outs[k].dst, w.pin_out + cur, sz[outs[k].seg] * sizeof(double));
+    cur += sz[outs[k].seg];
   }
   return ASLR_OK;
 }

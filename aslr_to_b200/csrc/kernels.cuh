@@ -4,6 +4,8 @@
 
 #include <cuda_runtime.h>
 
+#include <mutex>
+
 #include "backward_dev.cuh"
 #include "rollout_coop.cuh"
 
@@ -333,20 +335,25 @@ inline int launch_status() { return cudaGetLastError() == cudaSuccess ? 0 : -2; 
 
 // Opt a kernel in to more than 48 KB of dynamic shared memory, once per kernel and device (the attribute
 // sticks; setting it before every launch was a measurable share of the host's enqueue time once aslr_solve
-// started feeding several streams).
+// started feeding several streams).  The table is process-global and shared by every handle, so it is guarded by
+// a mutex (two host threads may drive different handles / GPUs); a failed opt-in is reported to the caller
+// instead of surfacing later as an opaque launch error.
 template <class Kernel>
-inline void allow_smem(Kernel k, size_t bytes) {
+inline int allow_smem(Kernel k, size_t bytes) {
   // keyed by the kernel's address (kernels of equal signature share this instantiation) and the device
   struct Entry { const void* fn; int dev; int bytes; };
   static Entry seen[64];
   static int n_seen = 0;
+  static std::mutex mu;
   int dev = 0;
-  cudaGetDevice(&dev);
+  if (cudaGetDevice(&dev) != cudaSuccess) return -2;
   const void* fn = reinterpret_cast<const void*>(k);
+  std::lock_guard<std::mutex> lock(mu);
   for (int i = 0; i < n_seen; ++i)
-    if (seen[i].fn == fn && seen[i].dev == dev && seen[i].bytes >= (int)bytes) return;
-  cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (seen[i].fn == fn && seen[i].dev == dev && seen[i].bytes >= (int)bytes) return 0;
+  if (cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess) return -2;
   if (n_seen < 64) seen[n_seen++] = Entry{fn, dev, (int)bytes};
+  return 0;
 }
 
 template <int N, bool VSA>
@@ -366,7 +373,7 @@ struct Launch {
     const unsigned blocks = (unsigned)((total + threads - 1) / threads);
     if (diff) {
       if (N <= ASLR_K1_STAGE_MAXN)
-        allow_smem(knot_kernel<N, NU, VSA, true>, stage_bytes(threads));
+        if (allow_smem(knot_kernel<N, NU, VSA, true>, stage_bytes(threads))) return -2;
       knot_kernel<N, NU, VSA, true><<<blocks, threads, stage_bytes(threads), s>>>(P, a);
     }
     else
@@ -378,7 +385,7 @@ struct Launch {
     const long total = (long)a.B * (a.T + 1);
     const int threads = 128;
     if (N <= ASLR_K1_STAGE_MAXN)
-      allow_smem(solver_calcdiff_kernel<N, NU, VSA>, stage_bytes(threads));
+      if (allow_smem(solver_calcdiff_kernel<N, NU, VSA>, stage_bytes(threads))) return -2;
     solver_calcdiff_kernel<N, NU, VSA>
         <<<(unsigned)((total + threads - 1) / threads), threads, stage_bytes(threads), s>>>(P, a);
     return launch_status();
@@ -390,7 +397,7 @@ struct Launch {
       constexpr int GS = ASLR_ROLLC_GS, TRIALS = ASLR_ROLLC_TRIALS;
       constexpr size_t bytes = sizeof(double) * (ModelConst<N>::SIZE + (size_t)TRIALS * RollSmem<N, NU>::SIZE);
       auto k = rollout_coop_kernel<N, NU, VSA, GS, TRIALS>;
-      allow_smem(k, bytes);
+      if (allow_smem(k, bytes)) return -2;
       k<<<(unsigned)((total + TRIALS - 1) / TRIALS), GS * TRIALS, bytes, s>>>(P, a, -1);
       if (launch_status()) return -2;
       trial_cost_kernel<N, NU, VSA><<<(unsigned)(((long)a.B * 32 + 127) / 128), 128, 0, s>>>(P, a, 0);
@@ -420,30 +427,30 @@ struct Launch {
       constexpr int GROUPS = ASLR_BWD_COLS_GROUPS;
       constexpr size_t slice = sizeof(double) * ColsSmem<NX, NU>::SIZE;
       auto k = backward_cols_kernel<NX, NU, GROUPS>;
-      allow_smem(k, slice * GROUPS);
+      if (allow_smem(k, slice * GROUPS)) return -2;
       k<<<(a.B + GROUPS - 1) / GROUPS, NX * GROUPS, slice * GROUPS, s>>>(a, lim);
     } else if constexpr (NX > 16 && NX <= 32 && NU <= 8 && ASLR_BWD_ROWS) {
       // (the box QP of SolverBoxDDP stays with the CTA-per-OCP sweep)
       if (!(a.opts.kind == ASLR_SOLVER_BOXDDP && P.has_limits)) {
         constexpr size_t bytes = sizeof(double) * RowsSmem<NX, NU>::SIZE;
         auto k = backward_rows_kernel<NX, NU>;
-        allow_smem(k, bytes);
+        if (allow_smem(k, bytes)) return -2;
         k<<<a.B, 32, bytes, s>>>(a);
         return launch_status();
       }
       constexpr int THREADS = ASLR_BWD_CTA_THREADS;
       auto k = backward_cta_kernel<NX, NU, THREADS>;
-      allow_smem(k, per);
+      if (allow_smem(k, per)) return -2;
       k<<<a.B, THREADS, per, s>>>(a, lim);
     } else if constexpr (NX <= 12) {
       constexpr int GS = ASLR_BWD_GS, GROUPS = 128 / GS;
       auto k = backward_warp_kernel<NX, NU, GS, GROUPS>;
-      allow_smem(k, per * GROUPS);
+      if (allow_smem(k, per * GROUPS)) return -2;
       k<<<(a.B + GROUPS - 1) / GROUPS, GS * GROUPS, per * GROUPS, s>>>(a, lim);
     } else {
       constexpr int THREADS = ASLR_BWD_CTA_THREADS;
       auto k = backward_cta_kernel<NX, NU, THREADS>;
-      allow_smem(k, per);
+      if (allow_smem(k, per)) return -2;
       k<<<a.B, THREADS, per, s>>>(a, lim);
     }
     return launch_status();
@@ -460,8 +467,14 @@ struct Launch {
   }
 };
 
-// defined in inst_n*.cu
+// defined in inst_n*.cu: one translation unit per link DOF (the reference's classes work for any pinModel.nv,
+// python/aslr_to/statemultibody_aslr.py:14-16; the kernels are compile-time sized, so "any" is 1..ASLR_MAX_DOF)
+Launchers launchers_n1(bool vsa);
 Launchers launchers_n2(bool vsa);
+Launchers launchers_n3(bool vsa);
+Launchers launchers_n4(bool vsa);
+Launchers launchers_n5(bool vsa);
+Launchers launchers_n6(bool vsa);
 Launchers launchers_n7(bool vsa);
 int launch_init(const SolverArgs& a, cudaStream_t s);
 int launch_accept(const SolverArgs& a, cudaStream_t s);

@@ -146,6 +146,29 @@ ASLR_HD double cost_terms(const DevCostSum<N>& C, const double* x, const double*
           acc.Lxxd[NX > 5 ? 5 : 0] += w * aw[5];
         }
       }
+    } else if (t.kind == ASLR_COST_RESIDUAL_DOUBLE_PENDULUM) {
+      // CostModelResidual over python/aslr_to/residual_acrobot.py:9-21 (n = 2 only; checked at problem creation):
+      // r = [s1, s2, 1 + c1, 1 - c2, x4, x5], Rx[0:2,0:2] = diag(c1, c2), Rx[2:4,0:2] = diag(-s1, +s2),
+      // Rx[4:6,4:6] = I; Lx = Rx^T (w r), Lxx = Rx^T diag(w) Rx (diagonal: every residual sees one state)
+      if (N == 2) {
+        double s1, c1, s2, c2;
+        sincos(x[0], &s1, &c1);
+        sincos(x[1], &s2, &c2);
+        const double r0 = s1, r1 = s2, r2 = 1 + c1, r3 = 1 - c2, r4 = x[NX > 4 ? 4 : 0], r5 = x[NX > 5 ? 5 : 0];
+        const double* aw = t.act;
+        cost += w * (0.5 * (aw[0] * r0 * r0 + aw[1] * r1 * r1 + aw[2] * r2 * r2 + aw[3] * r3 * r3 + aw[4] * r4 * r4 +
+                            aw[5] * r5 * r5));
+        if (DIFF) {
+          acc.Lx[0] += w * (c1 * (aw[0] * r0) - s1 * (aw[2] * r2));
+          acc.Lx[1] += w * (c2 * (aw[1] * r1) + s2 * (aw[3] * r3));
+          acc.Lx[NX > 4 ? 4 : 0] += w * (aw[4] * r4);
+          acc.Lx[NX > 5 ? 5 : 0] += w * (aw[5] * r5);
+          acc.Lxxd[0] += w * (c1 * c1 * aw[0] + s1 * s1 * aw[2]);
+          acc.Lxxd[1] += w * (c2 * c2 * aw[1] + s2 * s2 * aw[3]);
+          acc.Lxxd[NX > 4 ? 4 : 0] += w * aw[4];
+          acc.Lxxd[NX > 5 ? 5 : 0] += w * aw[5];
+        }
+      }
     }
   }
   return cost;

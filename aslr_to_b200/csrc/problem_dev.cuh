@@ -25,7 +25,7 @@ struct DevCostTerm {
   int frame_parent;
   double weight;
   double ref[(4 * N > 12) ? 4 * N : 12];
-  double act[4 * N];
+  double act[(4 * N > 6) ? 4 * N : 6];  // activation weights: ndx for the state residual, 6 for placement / pendulum
   double fR[9];
   double fp[3];
 };
@@ -74,7 +74,8 @@ inline void fill_cost_sum(const AslrCostSum& src, DevCostSum<N>& dst) {
     d.weight = s.weight;
     const int nref = (4 * N > 12) ? 4 * N : 12;
     for (int i = 0; i < nref; ++i) d.ref[i] = s.ref[i];
-    for (int i = 0; i < 4 * N; ++i) d.act[i] = s.act[i];
+    const int nact = (4 * N > 6) ? 4 * N : 6;
+    for (int i = 0; i < nact; ++i) d.act[i] = s.act[i];
     for (int i = 0; i < 9; ++i) d.fR[i] = s.frame.R[i];
     for (int i = 0; i < 3; ++i) d.fp[i] = s.frame.p[i];
   }

@@ -31,7 +31,7 @@ ASLR_HD void init_body(const SolverArgs& a, int b) {
   s.d1 = 0, s.d2 = 0, s.dg = 0, s.dq = 0, s.ffeas = 0;
   s.iter = 0, s.status = ASLR_OCP_RUNNING, s.is_feasible = a.opts.is_feasible ? 1 : 0, s.was_feasible = 0;
   s.recalc = 1, s.accepted = -1, s.src_slot = -1, s.n_backward_retries = 0;
-  s.full_steps = 0, s.reserved0 = 0;
+  s.full_steps = 0, s.n_logged = 0;
   if (b == 0) a.buf.counters[0] = a.B;
 }
 
@@ -554,6 +554,7 @@ ASLR_HD void accept_body(const SolverArgs& a, int b, int* n_done) {
   }
   s.iter = a.iter;
   if (!finished) {
+    s.n_logged = a.iter + 1;
     if (a.buf.log) {
       double* lg = a.buf.log + ((size_t)b * o.maxiter + a.iter) * ASLR_LOG_FIELDS;
       lg[0] = s.cost, lg[1] = s.stop, lg[2] = s.xreg, lg[3] = s.steplength, lg[4] = s.dV, lg[5] = s.dVexp;

@@ -45,6 +45,19 @@ def double_pendulum():
                 u_lb=None, u_ub=None)
 
 
+def double_pendulum_residual():
+    """examples/double_pendulum.py with the swing-up cost expressed through the package's residual model
+    (python/aslr_to/residual_acrobot.py:5-29, exported at __init__.py:9; no example uses it) under crocoddyl's
+    CostModelResidual + weighted-quad activation: residual `1 - c2`, Gauss-Newton Hessian."""
+    w = double_pendulum()
+    for terms in (w["running"], w["terminal"]):
+        for t in terms:
+            if t["kind"] == "pendulum":
+                t["kind"] = "pendulum_residual"
+    w["name"] = "double_pendulum_residual"
+    return w
+
+
 def two_dof_sea():
     """examples/two_dof_sea.py:18-81."""
     n, nu = 2, 2
@@ -133,6 +146,38 @@ def chain7_batch(B=1024, T=200, seed=20240002):
                 solver="fddp", th_stop=1e-7, maxiter=100, init="x0-zero-u", u_lb=None, u_ub=None)
 
 
+def chain_batch(n, B=2, T=12, seed=20240004, kind="sea"):
+    """The first n links of the 7-link arm (fixtures chain1 ... chain6, tools/make_robots.py) with chain7's cost
+    structure: one workload per link DOF the kernels are instantiated for.  kind = "vsa": SolverBoxDDP with an
+    initially active stiffness bound, as chain7_vsa_batch."""
+    if n == 7:
+        return chain7_batch(B, T, seed) if kind == "sea" else chain7_vsa_batch(B, T, seed)
+    rng = np.random.default_rng(seed + n)
+    q0 = rng.uniform(-1.0, 1.0, size=(B, n))
+    x0 = np.zeros((B, 4 * n))
+    x0[:, :n] = q0
+    x0[:, n:2 * n] = q0
+    reach = 0.3 * n
+    targets = np.stack([rng.uniform(0.2, 0.6, B) * reach, rng.uniform(-0.4, 0.4, B) * reach,
+                        rng.uniform(0.4, 0.9, B) * reach], axis=1)
+    mref = np.zeros((B, 12))
+    mref[:, :9] = np.eye(3).reshape(9)
+    mref[:, 9:] = targets
+    nu = n if kind == "sea" else 2 * n
+    running = _sorted([
+        _placement("gripperPose", 1e-1, "tip", targets[0]),
+        _term("xReg", "state", 1e-3, np.zeros(4 * n), np.array([1.0] * n + [0] * n + [1.0] * n + [0] * n)),
+        _term("uReg", "control", 1e-2, np.zeros(nu), np.ones(nu))])
+    terminal = [_placement("gripperPose", 1e4, "tip", targets[0])]
+    w = dict(name="chain%d_batch_%d" % (n, B), robot="chain%d" % n, gravity=None, kind=kind,
+             K=50.0 * np.eye(n) if kind == "sea" else None, B=0.05 * np.eye(n), Sm=None, dt=1e-2, T=T, x0=x0,
+             mref_ocp=mref, running=running, terminal=terminal, solver="fddp" if kind == "sea" else "boxddp",
+             th_stop=1e-7, maxiter=100, init="x0-zero-u", u_lb=None, u_ub=None)
+    if kind == "vsa":
+        w.update(u_lb=np.array([-50.0] * n + [5.0] * n), u_ub=np.array([50.0] * n + [100.0] * n))
+    return w
+
+
 def chain7_vsa_batch(B=2, T=20, seed=20240003):
     """7-link variable-stiffness arm under SolverBoxDDP (nx = 28, nu = 14): the 7-DOF counterpart of
     examples/two_dof_vsa_boxddp.py, with the stiffness bound starting active (sigma_lb > initial guess)."""
@@ -145,7 +190,8 @@ def chain7_vsa_batch(B=2, T=20, seed=20240003):
 
 # ------------------------------------------------------------------------------------------------
 _KIND = {"placement": A.COST_FRAME_PLACEMENT, "state": A.COST_STATE, "control": A.COST_CONTROL,
-         "stiffness": A.COST_STIFFNESS, "pendulum": A.COST_DOUBLE_PENDULUM}
+         "stiffness": A.COST_STIFFNESS, "pendulum": A.COST_DOUBLE_PENDULUM,
+         "pendulum_residual": A.COST_RESIDUAL_DOUBLE_PENDULUM}
 
 
 def frame_of(robot_dict, name):

@@ -11,9 +11,10 @@ host buffers, and the CPU oracle timed on the host cores.
   python bench.py [--gpus N] [--steps K] [--warmup W]          our CUDA path
   python bench.py --impl reference ...                          the reference-equivalent CPU path
 
-Multi-GPU (weak scaling): one process per GPU under torchrun, every rank solves its own 4096-OCP batch
-(seed + rank); there is no per-iteration collective, only a final NCCL all-gather of costs, iteration
-counts and trajectories (inside the timed region).
+Multi-GPU (STRONG scaling, the configuration BASELINE.json configs[3] names): one process per GPU under torchrun,
+the ONE 4096-OCP batch is cut into contiguous shards of 4096 / N OCPs (aslr_to_b200/sharding.py); there is no
+per-iteration collective, only a final NCCL all-gather of costs, iteration counts and trajectories to every rank
+(inside the timed region).  `--scaling weak` keeps round 1's replica mode (4096 OCPs per GPU, seed + rank).
 """
 import argparse
 import json
@@ -31,19 +32,25 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 METRIC = "batched_fddp_ocp_iters_per_s"
 UNIT = "OCP-iterations/s"
-B_PER_GPU = 4096
+B_TOTAL = 4096  # BASELINE.json configs[3]
+B_PER_GPU = B_TOTAL  # weak mode: every rank solves a batch of this size
 SEED = 20240001
-K1_DRAM_TRAFFIC_PER_LAUNCH = 785.1e6  # dram__bytes_read + write of one knot_kernel launch, ncu --set full (profiles/r01e_ncu_full.md)
 ALGO_BYTES_PER_KNOT = 1544  # 2-DOF SEA, read x,u; write xnext,cost,Fx,Fu,Lx,Lu,Lxx,Lxu,Luu
 
 
-def workload_config(n_gpus, solver="fddp"):
-    return {"workload": "4096 x 2-DOF SEA %s reaching OCPs per GPU (BASELINE.json configs[3]), T=100, "
-                        "th_stop=1e-7, maxiter=100, solved to convergence" % solver.upper(),
-            "ocps_per_gpu": B_PER_GPU, "T": 100, "nx": 8, "nu": 2, "solver": solver,
-            "parallelism": "independent OCPs sharded over %d GPU(s), no per-iteration collective" % n_gpus,
-            "l2": "per-iteration working set (derivative records 576 MB + trial trajectories 331 MB per GPU) "
-                  "exceeds the 126 MB L2, no explicit flush"}
+def workload_config(n_gpus, solver="fddp", scaling="strong"):
+    per = B_TOTAL // n_gpus if scaling == "strong" else B_PER_GPU
+    total = B_TOTAL if scaling == "strong" else B_PER_GPU * n_gpus
+    return {"workload": "%d x 2-DOF SEA %s reaching OCPs in total, %d per GPU (BASELINE.json configs[3]), T=100, "
+                        "th_stop=1e-7, maxiter=100, solved to convergence" % (total, solver.upper(), per),
+            "ocps_total": total, "ocps_per_gpu": per, "T": 100, "nx": 8, "nu": 2, "solver": solver,
+            "parallelism": "one batch of independent OCPs cut into %d contiguous shard(s), no per-iteration collective, "
+                           "final NCCL all-gather of trajectories and solver state inside the timed region" % n_gpus
+                           if scaling == "strong" else
+                           "replicas: every GPU solves its own %d-OCP batch (seed + rank)" % B_PER_GPU,
+            "l2": "per-iteration working set of a 4096-OCP shard (derivative records + trial trajectories, > 500 MB) "
+                  "exceeds the 126 MB L2, no explicit flush; smaller shards (N >= 4) fit in L2 and say so by being "
+                  "timed as they are: the same bytes are re-written by every iteration"}
 
 
 # ------------------------------------------------------------------------------------ clocks
@@ -97,27 +104,35 @@ class ClockSampler(object):
 
 # ------------------------------------------------------------------------------ CPU baselines
 def _cpu_worker(args):
-    b, seed = args
+    """Solves the OCPs `bs` of the batch with the oracle; returns (iterations, seconds spent in the solves alone:
+    process start-up, imports and building the workload are not part of the rate)."""
+    bs, seed = args
     import oracle_build as ob
     from aslr_to_b200 import workloads as W
-    w = W.sea_batch(B_PER_GPU, seed=seed)
-    t0 = time.perf_counter()
-    solver, log = ob.solve(w, b, "port")
-    return len(log.costs), time.perf_counter() - t0
+    w = W.sea_batch(B_TOTAL, seed=seed)
+    iters, t = 0, 0.0
+    for b in bs:
+        t0 = time.perf_counter()
+        solver, log = ob.solve(w, b, "port")
+        t += time.perf_counter() - t0
+        iters += len(log.costs)
+    return iters, t
 
 
-def cpu_oracle_rate(n_ocps, procs, seed=SEED):
-    """OCP-iterations/s of the NumPy oracle (reference-equivalent CPU path) on `procs` host cores."""
+def cpu_oracle_rate(n_ocps, procs, seed=SEED, pool=None):
+    """OCP-iterations/s of the NumPy oracle (reference-equivalent CPU path) on `procs` host cores: OCPs 0..n_ocps-1
+    of the batch dealt round-robin to the workers; rate = iterations / the busiest worker's solve time."""
     import multiprocessing as mp
-    jobs = [(b, seed) for b in range(n_ocps)]
-    t0 = time.perf_counter()
+    jobs = [(list(range(k, n_ocps, procs)), seed) for k in range(procs)]
+    jobs = [j for j in jobs if j[0]]
     if procs == 1:
-        res = [_cpu_worker(j) for j in jobs]
+        res = [_cpu_worker(jobs[0])]
+    elif pool is not None:
+        res = pool.map(_cpu_worker, jobs)
     else:
-        with mp.get_context("spawn").Pool(procs) as pool:
-            res = pool.map(_cpu_worker, jobs)
-    wall = time.perf_counter() - t0
-    iters = sum(r[0] for r in res)
+        with mp.get_context("spawn").Pool(procs) as pl:
+            res = pl.map(_cpu_worker, jobs)
+    iters, wall = sum(r[0] for r in res), max(r[1] for r in res)
     return iters / wall, iters, wall
 
 
@@ -159,25 +174,28 @@ def cpu_cxx_rate(n_ocps, procs=1, seed=SEED):
 def run_reference(args):
     """--impl reference: the reference's CPU algorithm (oracle port: the reference's model maths on the
     NumPy restatement of crocoddyl/pinocchio -- the originals cannot be built here) on all
-    host cores; each step is a bounded sample (one OCP per core) of the same workload."""
+    host cores; each step is a bounded sample (one OCP per core) of the same workload.  The workers are started
+    once; a step's time is the busiest worker's time inside its solves."""
+    import multiprocessing as mp
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    for _ in range(args.warmup if args.warmup < 1 else 1):
-        cpu_oracle_rate(cores, cores)
     t_total, it_total = 0.0, 0
-    for _ in range(args.steps):
-        rate, iters, wall = cpu_oracle_rate(cores, cores)
-        t_total += wall
-        it_total += iters
+    with mp.get_context("spawn").Pool(cores) as pool:
+        for _ in range(args.warmup):
+            cpu_oracle_rate(cores, cores, pool=pool)
+        for _ in range(args.steps):
+            rate, iters, wall = cpu_oracle_rate(cores, cores, pool=pool)
+            t_total += wall
+            it_total += iters
     value = it_total / t_total
     sample = "%d OCPs (one per core) of the 4096-OCP batch per step, full FDDP solve each" % cores
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * t_total / max(args.steps, 1),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args.gpus),
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / max(args.steps, 1),
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.gpus, scaling=args.scaling),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
@@ -185,6 +203,7 @@ def run_reference(args):
 
 # -------------------------------------------------------------------------------- our CUDA arm
 def run_ours(args):
+    import ctypes as C
     import torch
     import torch.distributed as dist
     from aslr_to_b200 import _abi as A, batched as BT, sharding as S, workloads as W
@@ -203,37 +222,46 @@ def run_ours(args):
             os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
 
-    w = W.sea_batch(B_PER_GPU, seed=SEED + rank, solver=args.solver)
-    B, T, nx, nu = B_PER_GPU, w["T"], 8, 2
-    prob = BT.BatchedShootingProblem(W.to_desc(w), w["x0"], T, K_ocp=w["K_ocp"], device=dev)
-    solver = BT.BatchedSolver(prob, W.SOLVER_KIND[args.solver], maxiter=w["maxiter"], th_stop=w["th_stop"], store_vxx=False,
+    strong = args.scaling == "strong"
+    if strong:  # BASELINE.json configs[3]: ONE 4096-OCP batch, contiguous shards of 4096 / N (sharding.py)
+        w = S.shard_workload(W.sea_batch(B_TOTAL, seed=SEED, solver=args.solver), world, rank)
+        B_all = B_TOTAL
+    else:       # replicas: every rank its own batch
+        w = W.sea_batch(B_PER_GPU, seed=SEED + rank, solver=args.solver)
+        B_all = B_PER_GPU * world
+    B, T, nx, nu = int(np.asarray(w["x0"]).shape[0]), w["T"], 8, 2
+    desc = W.to_desc(w)
+    kind = W.SOLVER_KIND[args.solver]
+    prob = BT.BatchedShootingProblem(desc, w["x0"], T, K_ocp=w["K_ocp"], device=dev)
+    solver = BT.BatchedSolver(prob, kind, maxiter=w["maxiter"], th_stop=w["th_stop"], store_vxx=False,
                               store_quu=False, store_log=False)
     xs0_h, us0_h = initial_guess_arrays(w, np.asarray(w["x0"]), T, nu)
-    # pinned host buffers = what a caller of the public API holds
-    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    # pinned host buffers = what a caller of the host-pointer C ABI holds
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).pin_memory()
     h_x0, h_K, h_xs0, h_us0 = pin(w["x0"]), pin(np.asarray(w["K_ocp"]).reshape(B, 4)), pin(xs0_h), pin(us0_h)
     d_xs0, d_us0 = h_xs0.to(dev), h_us0.to(dev)
     h_xs = torch.empty((B, T + 1, nx), dtype=torch.float64).pin_memory()
     h_us = torch.empty((B, T, nu), dtype=torch.float64).pin_memory()
     h_state = torch.empty((B, A.OCP_STATE_DOUBLES), dtype=torch.float64).pin_memory()
+    # second handle for the end-to-end path: aslr_solve_host owns its device workspace and does every copy itself
+    lib = prob.lib
+    e2e_handle = C.c_void_p()
+    A.check(lib.aslr_problem_create(C.byref(desc), C.byref(e2e_handle)))
+    e2e_result = {}
 
     def step_device():
         solver.t["xs"].copy_(d_xs0)
         solver.t["us"].copy_(d_us0)
         solver.solve(set_candidate=False)
         if world > 1:  # the only collective of the path: final gather of costs / iterations / trajectories
-            S.gather_results({k: solver.t[k] for k in ("xs", "us", "state")}, B * world)
+            S.gather_results({k: solver.t[k] for k in ("xs", "us", "state")}, B_all)
 
     def step_e2e():
-        prob.x0.copy_(h_x0, non_blocking=True)
-        prob.K_ocp.copy_(h_K, non_blocking=True)
-        solver.t["xs"].copy_(h_xs0, non_blocking=True)
-        solver.t["us"].copy_(h_us0, non_blocking=True)
-        solver.solve(set_candidate=False)
-        h_xs.copy_(solver.t["xs"], non_blocking=True)
-        h_us.copy_(solver.t["us"], non_blocking=True)
-        h_state.copy_(solver.t["state"], non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        # the reference-facing call with HOST buffers: x0 / K / warm start in, xs / us / solver state out, the
+        # host <-> device copies inside the call (include/aslr_b200.h: aslr_solve_host)
+        e2e_result["r"] = BT.solve_host(desc, h_x0, T, kind, xs=h_xs0, us=h_us0, maxiter=w["maxiter"],
+                                        th_stop=w["th_stop"], K_ocp=h_K, out={"xs": h_xs, "us": h_us, "state": h_state},
+                                        handle=e2e_handle, lib=lib)
 
     def barrier():
         if world > 1:
@@ -249,6 +277,20 @@ def run_ours(args):
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    def timed_wall(fn, steps):
+        """host-side clock around a blocking host-pointer call (its copies and kernels run on the library's own
+        stream, which torch's events do not see); barrier + synchronize on both sides, max over ranks"""
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            fn()
+        torch.cuda.synchronize()
+        ms = torch.tensor([(time.perf_counter() - t0) * 1e3], dtype=torch.float64, device=dev)
+        barrier()
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
@@ -269,7 +311,7 @@ def run_ours(args):
         idx = np.nonzero(solver.states()["status"] != A.OCP_CONVERGED)[0]
         x0f, Kf = np.asarray(w["x0"])[idx], np.asarray(w["K_ocp"])[idx]
         probf = BT.BatchedShootingProblem(W.to_desc(w), x0f, T, K_ocp=Kf, device=dev)
-        solf = BT.BatchedSolver(probf, W.SOLVER_KIND[args.solver], maxiter=w["maxiter"], th_stop=w["th_stop"],
+        solf = BT.BatchedSolver(probf, kind, maxiter=w["maxiter"], th_stop=w["th_stop"],
                                 store_vxx=False, store_quu=False, store_log=False)
         xf, uf = initial_guess_arrays(w, x0f, T, nu)
         for _ in range(2):
@@ -285,35 +327,47 @@ def run_ours(args):
     iters_per_solve = int(np.sum(st["iter"] + (st["status"] == A.OCP_CONVERGED)))
     n_conv = int(np.sum(st["status"] == A.OCP_CONVERGED))
     launches_per_step = int(solver.result.kernel_launches)
-    tot = torch.tensor([float(iters_per_solve)], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(iters_per_solve), float(n_conv)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tot)
-    total_iters = float(tot.item())
+    total_iters, total_conv = float(tot[0].item()), int(tot[1].item())
+    step_e2e()  # warm-up of the host-pointer path (allocates its workspace)
+    step_e2e()
+    st_e2e = e2e_result["r"]["states"]
+    assert np.array_equal(st_e2e["iter"], st["iter"]) and np.array_equal(st_e2e["cost"], st["cost"]), \
+        "the host-pointer path and the device-pointer path disagree"
 
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     ms = timed(step_device, args.steps)
-    ms_e2e = timed(step_e2e, args.steps)
+    ms_e2e = timed_wall(step_e2e, args.steps)
     value = total_iters * args.steps / (ms * 1e-3)
     e2e_value = total_iters * args.steps / (ms_e2e * 1e-3)
 
-    # ---- dominant-kernel roofline: the fused calc+calcDiff sweep over the batch's B*(T+1) knots
+    # ---- the metric's second half: the fused calc+calcDiff sweep over the shard's B*(T+1) knots
     xs_sol, us_sol = solver.t["xs"].clone(), solver.t["us"].clone()
     out = A.KnotOut()
     out.xnext, out.cost, out.deriv = solver.t["xnext"].data_ptr(), solver.t["knot_cost"].data_ptr(), \
         solver.t["deriv"].data_ptr()
     bs = prob.batch_struct()
-    import ctypes as C
     stream = prob._stream()
 
-    def calcdiff_sweep():
-        A.check(prob.lib.aslr_calc_diff(prob.handle, C.byref(bs), xs_sol.data_ptr(), us_sol.data_ptr(), C.byref(out),
-                                        stream))
+    def calcdiff_sweep(xs_t=xs_sol, us_t=us_sol):
+        A.check(lib.aslr_calc_diff(prob.handle, C.byref(bs), xs_t.data_ptr(), us_t.data_ptr(), C.byref(out), stream))
     for _ in range(3):
         calcdiff_sweep()
     reps = 20
     ms_k1 = timed(lambda: calcdiff_sweep(), reps) / reps
+    # the same sweep on random states: x ~ U(-pi, pi)^2n x U(-2, 2)^2n, u ~ U(-1, 1)
+    g = torch.Generator(device=dev)
+    g.manual_seed(SEED + rank)
+    xs_rnd = torch.cat([(torch.rand((B, T + 1, 4), generator=g, device=dev, dtype=torch.float64) * 2 - 1) * np.pi,
+                        (torch.rand((B, T + 1, 4), generator=g, device=dev, dtype=torch.float64) * 2 - 1) * 2.0], dim=2)
+    us_rnd = torch.rand((B, T, nu), generator=g, device=dev, dtype=torch.float64) * 2 - 1
+    for _ in range(3):
+        calcdiff_sweep(xs_rnd, us_rnd)
+    ms_k1_rnd = timed(lambda: calcdiff_sweep(xs_rnd, us_rnd), reps) / reps
     clocks = sampler.stop() if rank == 0 else None
     knots = B * (T + 1)
     knots_per_s = knots * world / (ms_k1 * 1e-3)
@@ -326,36 +380,35 @@ def run_ours(args):
     achieved = ALGO_BYTES_PER_KNOT * knots / (ms_k1 * 1e-3) / 1e9
 
     # ---- where one solve spends its time: CUDA events around every stage of one more solve (untimed extra)
-    rows = np.array(stage_event_times(prob, solver, w, w["maxiter"], W.SOLVER_KIND[args.solver]))
-    stage_ms = rows.sum(0) * 1e-3
-    stages = {"ms_per_solve": dict(zip(STAGES, [round(float(v), 3) for v in stage_ms])),
-              "share": dict(zip(STAGES, [round(float(v / stage_ms.sum()), 3) for v in stage_ms])),
-              "full_batch_us": dict(zip(STAGES, [float(v) for v in rows[1]])),
-              "floor_us": dict(zip(STAGES, [float(v) for v in rows[-1]])),
-              "fp64_pipe_frac_ncu": {"calcdiff": 0.26, "backward": 0.21, "rollout": 0.22},
-              "note": "stepwise ABI with one event pair and one sync per stage, after the timed region; full_batch = "
-                      "iteration 1, floor = last iteration (stragglers only); FP64-pipe utilisation of each kernel at "
-                      "full batch from profiles/r01e_ncu_full.md (rollout: the alpha = 1 phase of a mid-solve iteration, profiles/r01g_ncu_full_rollout.md; measured FP64 peak 34.2 TFLOP/s)"}
+    stages = None
+    if rank == 0:
+        rows = np.array(stage_event_times(prob, solver, w, w["maxiter"], kind))
+        stage_ms = rows.sum(0) * 1e-3
+        stages = {"ms_per_solve": dict(zip(STAGES, [round(float(v), 3) for v in stage_ms])),
+                  "share": dict(zip(STAGES, [round(float(v / stage_ms.sum()), 3) for v in stage_ms])),
+                  "full_batch_us": dict(zip(STAGES, [float(v) for v in rows[1]])),
+                  "floor_us": dict(zip(STAGES, [float(v) for v in rows[-1]])),
+                  "note": "stepwise ABI with one event pair and one sync per stage, after the timed region; full_batch = "
+                          "iteration 1, floor = last iteration (stragglers only)"}
+    if world > 1:
+        barrier()
 
     if rank == 0:
         line = {
             "metric": METRIC.replace("fddp", args.solver), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(world, args.solver),
-            "ocp_iters_per_solve_all_gpus": total_iters, "converged_rank0": n_conv,
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(world, args.solver, args.scaling),
+            "ocp_iters_per_solve_all_gpus": total_iters, "converged_all_gpus": total_conv,
             "calcdiff_knots_per_s": knots_per_s, "calcdiff_ms": ms_k1,
+            "calcdiff_random_states": {"knots_per_s": knots * world / (ms_k1_rnd * 1e-3), "ms": ms_k1_rnd,
+                                       "inputs": "x ~ U(-pi,pi)^4 x U(-2,2)^4, u ~ U(-1,1)^2 (SURVEY.md 8d config 4)"},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+                    "api": "aslr_solve_host (C ABI, host pointers; pinned caller memory used in place)",
                     "h2d_bytes_per_step": int(h_x0.nbytes + h_K.nbytes + h_xs0.nbytes + h_us0.nbytes),
                     "d2h_bytes_per_step": int(h_xs.nbytes + h_us.nbytes + h_state.nbytes)},
             "gpu_launches": launches_per_step * args.steps,
-            "roofline": {"kernel": "knot_kernel<2,2,SEA,DIFF> (fused calc+calcDiff, %d knots)" % knots,
-                         "bound": "hbm", "achieved": achieved, "peak": peak,
-                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": K1_DRAM_TRAFFIC_PER_LAUNCH,
-                         "traffic_source": "ncu --set full capture of this kernel, profiles/r01e_ncu_full.md",
-                         "fp64": {"dfma_latency_cycles": 8.2, "peak_tflops_measured": 34.2,
-                                  "source": "tools/fp64_peak.cu on this pool, profiles/r01b_fp64_peak.json"}},
+            "roofline": roofline_block(rank, knots, ms_k1, achieved, peak, peaks, stages),
             "clocks": clocks, "stages": stages,
         }
         if world == 1 and not args.no_cpu:
@@ -364,22 +417,103 @@ def run_ours(args):
                                     "sample": "%d OCPs of the same batch, full FDDP solve each (%d iterations, %.1f s)"
                                               % (args.cpu_ocps, iters, wall)}
             try:
-                kind = "this repository's solver source compiled for the host (g++ -O2), not the reference's code path"
+                what = "this repository's solver source compiled for the host (g++ -O2), not the reference's code path"
                 crate, citers, cwall = cpu_cxx_rate(32)
-                line["cpu_cxx"] = {"value": crate, "unit": UNIT, "cores": 1, "kind": kind,
+                line["cpu_cxx"] = {"value": crate, "unit": UNIT, "cores": 1, "kind": what,
                                    "sample": "32 OCPs of the same batch (%d iterations, %.1f s)" % (citers, cwall)}
                 cores = os.cpu_count() or 1
                 if cores > 1:
                     crate, citers, cwall = cpu_cxx_rate(32, cores)
                     line["cpu_cxx_all_cores"] = {
-                        "value": crate, "unit": UNIT, "cores": cores, "kind": kind,
+                        "value": crate, "unit": UNIT, "cores": cores, "kind": what,
                         "sample": "32 OCPs per core, %d processes (%d iterations, slowest worker %.1f s)"
                                   % (cores, citers, cwall)}
             except Exception as e:  # no host compiler on the box: the figure is optional
                 line["cpu_cxx"] = {"unavailable": str(e)[:120]}
+        if world == 1 and not args.no_extras:
+            # SURVEY.md section 8d extras, bounded: the SolverDDP line of config 4 and the config-5 MPC line
+            try:
+                line["extras"] = {"sea4096_ddp": extra_ddp_line(prob, w, d_xs0, d_us0),
+                                  "chain7_mpc": extra_chain7_line()}
+            except Exception as e:
+                line["extras"] = {"error": str(e)[:200]}
         print(json.dumps(line))
+    lib.aslr_problem_destroy(e2e_handle)
     if world > 1:
         dist.destroy_process_group()
+
+
+def roofline_block(rank, knots, ms_k1, achieved, peak, peaks, stages):
+    """Roofline of the fused calc+calcDiff sweep (the only HBM-shaped kernel of the path) plus, from the stage
+    timings, which stage dominates a solve.  ncu-derived figures (DRAM traffic per launch, FP64 pipe utilisation) are
+    read from profiles/ncu_figures.json, written by tools/ncu_summary.py together with the hash of the kernel sources
+    they were captured from; when the sources have changed since, they are withheld rather than quoted stale."""
+    figs, stale = {}, None
+    try:
+        figs = json.load(open(os.path.join(ROOT, "profiles", "ncu_figures.json")))
+        import __graft_entry__ as ge
+        if figs.get("source_hash") != ge._source_hash():
+            stale = "profiles/ncu_figures.json was captured from other kernel sources (%s): figures withheld" % \
+                    str(figs.get("source_hash"))[:12]
+    except Exception as e:
+        stale = "profiles/ncu_figures.json unavailable (%s)" % type(e).__name__
+    k1 = (figs.get("kernels", {}) or {}).get("knot_kernel", {}) if not stale else {}
+    block = {"kernel": "knot_kernel<2,2,SEA,DIFF> (fused calc+calcDiff, %d knots)" % knots,
+             "bound": "hbm", "achieved": achieved, "peak": peak,
+             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+             "unit": "GB/s", "frac": achieved / peak, "traffic": k1.get("dram_bytes_per_launch"),
+             "algorithmic_bytes_per_knot": ALGO_BYTES_PER_KNOT}
+    if stale:
+        block["ncu_figures"] = stale
+    else:
+        block["ncu_figures"] = {"source": "profiles/ncu_figures.json", "capture": figs.get("capture"),
+                                "kernels": figs.get("kernels")}
+    if stages:
+        dom = max(stages["share"], key=lambda k: stages["share"][k])
+        block["dominant_stage"] = {"stage": dom, "share_of_solve": stages["share"][dom],
+                                   "note": "K2 / K3 are time-sequential dependent chains (one knot after the other): "
+                                           "their bound is dependent-issue latency, not bytes or flops; see "
+                                           "stages.floor_us and DESIGN.md section 5"}
+    return block
+
+
+def extra_ddp_line(prob, w, d_xs0, d_us0, steps=3):
+    """SolverDDP on the same 4096-OCP batch ('Solver FDDP and DDP')."""
+    import torch
+    from aslr_to_b200 import _abi as A, batched as BT
+    solver = BT.BatchedSolver(prob, A.SOLVER_DDP, maxiter=w["maxiter"], th_stop=w["th_stop"], store_vxx=False,
+                              store_quu=False, store_log=False)
+
+    def step():
+        solver.t["xs"].copy_(d_xs0)
+        solver.t["us"].copy_(d_us0)
+        solver.solve(set_candidate=False)
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize()
+    st = solver.states()
+    iters = int(np.sum(st["iter"] + (st["status"] == A.OCP_CONVERGED)))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    return {"metric": "batched_ddp_ocp_iters_per_s", "value": iters / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms,
+            "ocp_iters_per_solve": iters, "converged": int(np.sum(st["status"] == A.OCP_CONVERGED)), "steps": steps,
+            "warmup": 2}
+
+
+def extra_chain7_line(steps=5, warmup=2):
+    """BASELINE.json configs[4] as an extra key of the default line (bounded: 2 warm-up + 5 MPC steps)."""
+    import argparse as ap
+    import io
+    import contextlib
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        run_chain7_mpc(ap.Namespace(chain7_ocps=1024, steps=steps, warmup=warmup))
+    return json.loads(buf.getvalue().strip().splitlines()[-1])
 
 
 def run_chain7_mpc(args):
@@ -493,6 +627,10 @@ def main():
     ap.add_argument("--workload", default="sea4096", choices=["sea4096", "chain7_mpc"])
     ap.add_argument("--chain7-ocps", type=int, default=1024)
     ap.add_argument("--solver", default="fddp", choices=["fddp", "ddp"], help="sea4096 workload: SolverFDDP (headline) or SolverDDP")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="strong (default, BASELINE.json configs[3]): one 4096-OCP batch cut into 4096 / N shards; "
+                         "weak: 4096 OCPs per GPU (round 1's replica mode)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the SolverDDP and chain7 MPC extra lines (N = 1 only)")
     args = ap.parse_args()
     # stdout carries exactly one JSON line.  Native libraries write banners to file descriptor 1 (NCCL prints its
     # version there whatever NCCL_DEBUG says on this pool): point fd 1 at stderr and keep Python's stdout on a

@@ -12,10 +12,11 @@
  *     last error of the calling thread is available from aslr_last_error(); nothing throws across
  *     the boundary;
  *   - all array arguments are DEVICE pointers to FP64 data owned by the caller (row-major,
- *     contiguous, 16-byte aligned), except in the *_host functions which take HOST pointers and do
- *     the copies themselves; `stream` is a cudaStream_t passed as void* (NULL = default stream);
+ *     contiguous, 16-byte aligned), except in aslr_solve_host which takes HOST pointers and does
+ *     the copies itself; `stream` is a cudaStream_t passed as void* (NULL = default stream);
  *     calls are asynchronous on that stream unless stated otherwise;
- *   - handles are not thread-safe: one handle per (process, GPU, stream);
+ *   - handles are not thread-safe: one handle per (process, GPU, stream); a handle belongs to the CUDA
+ *     device that was current at aslr_problem_create and every call runs on that device;
  *   - state layout x = [q_l | q_m | v_l | v_m] (python/aslr_to/statemultibody_aslr.py:7-11), n = link
  *     DOF, nx = ndx = 4n; only serial chains of revolute joints (nq == nv) are supported, which is
  *     what the reference's state manifold supports (statemultibody_aslr.py:52).
@@ -100,7 +101,10 @@ typedef enum AslrCostKind {
   /* CostModelStiffness (stiffness_cost.py:6-20): ref[0..n-1] = Kref, act[0] = lamda */
   ASLR_COST_STIFFNESS = 4,
   /* CostModelDoublePendulum (python/aslr_to/__init__.py:223-259): act[0..5] = activation weights */
-  ASLR_COST_DOUBLE_PENDULUM = 5
+  ASLR_COST_DOUBLE_PENDULUM = 5,
+  /* CostModelResidual(activation, ResidualModelDoublePendulum) (python/aslr_to/residual_acrobot.py:5-29):
+   * r = [s1, s2, 1 + c1, 1 - c2, v1, v2], Gauss-Newton Hessian; act[0..5] = activation weights (n = 2 only) */
+  ASLR_COST_RESIDUAL_DOUBLE_PENDULUM = 6
 } AslrCostKind;
 
 typedef struct AslrCostTerm {
@@ -183,7 +187,8 @@ typedef struct AslrOcpState {
   int32_t n_backward_retries;
   int32_t full_steps;  /* consecutive iterations that took the full step (alpha = 1); steers how many step
                           lengths the forward pass rolls out speculatively, never the result */
-  int32_t reserved0;
+  int32_t n_logged;    /* rows of `log` written for this OCP = iterations whose callbacks crocoddyl would have run
+                          (an iteration that ends with regularisation at reg_max returns before the callbacks) */
 } AslrOcpState;
 
 typedef enum AslrOcpStatus {
@@ -280,6 +285,27 @@ int aslr_accept_step(const AslrProblem* p, const AslrBatch* batch, const AslrSol
  * Synchronises `stream` before returning; `result` is a HOST pointer. */
 int aslr_solve(const AslrProblem* p, const AslrBatch* batch, const AslrSolverOpts* opts, const AslrSolverBuffers* buf,
                AslrSolveResult* result, void* stream);
+
+/* The same call with HOST buffers on both sides (what a crocoddyl user holds: numpy arrays of x0, the warm start
+ * xs / us, and room for the solution): solver.solve(xs, us, maxiter) of examples/two_dof_sea.py:77-81 for B OCPs,
+ * host -> device copies, the solve and device -> host copies all inside the call.  The handle owns the device
+ * workspace, a stream and pinned staging; page-locked caller memory is used in place, pageable memory is staged.
+ * Blocking.  Not thread-safe per handle. */
+typedef struct AslrHostSolveIO {
+  int32_t B, T;
+  const double* x0;       /* in  [B][nx] */
+  const double* K_ocp;    /* in  optional [B][n*n] */
+  const double* mref_ocp; /* in  optional [B][12] */
+  const double* xs_init;  /* in  [B][T+1][nx]; NULL = state.zero() at every knot (solve([], [], ...)) */
+  const double* us_init;  /* in  [B][T][nu];   NULL = zero controls */
+  double* xs;             /* out [B][T+1][nx] solver.xs */
+  double* us;             /* out [B][T][nu]   solver.us */
+  AslrOcpState* state;    /* out [B]          solver.cost / .stop / .iter / ... */
+  double* Kgain;          /* out optional [B][T][nu][nx] solver.K */
+  double* kff;            /* out optional [B][T][nu]     solver.k */
+  double* log;            /* out optional [B][maxiter][ASLR_LOG_FIELDS] (CallbackLogger) */
+} AslrHostSolveIO;
+int aslr_solve_host(AslrProblem* p, const AslrHostSolveIO* io, const AslrSolverOpts* opts, AslrSolveResult* result);
 
 #ifdef __cplusplus
 }

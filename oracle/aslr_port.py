@@ -9,7 +9,7 @@ Restated functions (file:line under /root/reference/python/aslr_to):
   euler_step / euler_jacobians        integrated_action.py:13-26 / :28-42
   PortState                           statemultibody_aslr.py:13-109 (vector-space joints only)
   cost terms                          residual_frame_placement.py:13-24, stiffness_cost.py:13-20,
-                                      __init__.py:229-249, + crocoddyl CostModelResidual over
+                                      __init__.py:229-249, residual_acrobot.py:9-21, + crocoddyl CostModelResidual over
                                       ResidualModelState / ResidualModelControl (Appendix A.5)
   motor-side actuation map Sm         actuation_asr.py:9-13, actuation_vsa.py:9-13, __init__.py:276-289
 It is written as plain functions over one flat problem spec (not class-by-class like the
@@ -28,7 +28,7 @@ import crocoddyl  # noqa: E402  (the NumPy shim)
 import pinocchio  # noqa: E402  (the NumPy shim)
 
 SEA, VSA = 0, 1
-FRAME_PLACEMENT, STATE, CONTROL, STIFFNESS, DOUBLE_PENDULUM = 1, 2, 3, 4, 5
+FRAME_PLACEMENT, STATE, CONTROL, STIFFNESS, DOUBLE_PENDULUM, RESIDUAL_DOUBLE_PENDULUM = 1, 2, 3, 4, 5, 6
 
 
 class Spec(object):
@@ -155,6 +155,19 @@ def cost_value_and_derivatives(spec, pdata, x, u, diff):
                 Lxx[1, 1] += w * ((c2 ** 2 - s2 ** 2) * a[1] + (s2 ** 2 + (1 - c2) * c2) * a[3])
                 Lxx[4, 4] += w * a[4]
                 Lxx[5, 5] += w * a[5]
+        elif kind == RESIDUAL_DOUBLE_PENDULUM:
+            # CostModelResidual(activation, ResidualModelDoublePendulum): residual_acrobot.py:9-21
+            s1, s2, c1, c2 = np.sin(x[0]), np.sin(x[1]), np.cos(x[0]), np.cos(x[1])
+            a = c["act"]
+            r = np.array([s1, s2, 1 + c1, 1 - c2, x[4], x[5]])
+            total += w * 0.5 * float(np.dot(a * r, r))
+            if diff:
+                Rx = np.zeros((6, nx))
+                Rx[:2, :2] = np.diag([c1, c2])
+                Rx[2:4, :2] = np.diag([-s1, s2])
+                Rx[4:6, 4:6] = np.eye(2)
+                Lx += w * (Rx.T @ (a * r))
+                Lxx += w * (Rx.T @ (a[:, None] * Rx))
         else:
             raise ValueError("unknown cost kind %r" % kind)
     return total, Lx, Lu, Lxx, Lxu, Luu

@@ -10,6 +10,10 @@ The fixtures travel to the GPU box; the reference does not.
                           running model, and the terminal model evaluated with u = None
   solve_<workload>.npz    full solver trace of the example (per-iteration cost, stop, x_reg, step, dV,
                           dVexp; final xs, us, K, k, Vx, Vxx, Qu; iteration count; converged flag)
+  solve_sea_batch_fddp_b924.npz   one of the two members of the 4096-OCP headline batch that never converge
+                          (924 and 3415: all 100 iterations, 43 % of the timed region of bench.py)
+  solve_chain7_T200_b<k>.npz      7-link arm at the bench's horizon T = 200: OCP 2 (converges, 50 iterations)
+                          and OCP 1 (does not converge in the bench's first solve; trace cut at 25 iterations)
 """
 import os
 import sys
@@ -76,7 +80,8 @@ def _have(path):
 def main():
     if not ob.refenv.have_reference():
         raise SystemExit("/root/reference is not available: golden vectors can only be made in the build container")
-    singles = [W.double_pendulum(), W.two_dof_sea(), W.two_dof_vsa_boxddp(), W.two_dof_vsa_modified()]
+    singles = [W.double_pendulum(), W.double_pendulum_residual(), W.two_dof_sea(), W.two_dof_vsa_boxddp(),
+               W.two_dof_vsa_modified()]
     c7 = W.chain7_batch(B=2, T=20)
     c7v = dict(c7, name="chain7_vsa", kind="vsa", K=None,
                running=[t for t in c7["running"] if t["kind"] != "control"] +
@@ -108,6 +113,25 @@ def main():
                                 **solver_trace(solver, log))
             print("solve sea_batch", solver_name, b, "iters", solver.iter, solver.converged,
                   "%.1fs" % (time.time() - t0))
+    # a member of the headline batch that stops at maxiter (found with the g++ build of the solver: 924, 3415)
+    path = os.path.join(HERE, "solve_sea_batch_fddp_b924.npz")
+    if not _have(path):
+        t0 = time.time()
+        solver, log = ob.solve(W.sea_batch(4096), 924, "reference")
+        np.savez_compressed(path, **solver_trace(solver, log))
+        print("solve sea_batch fddp 924 iters", solver.iter, solver.converged, "%.1fs" % (time.time() - t0))
+    # the 7-link arm at the bench's horizon
+    for b, maxiter in ((2, 100), (1, 25)):
+        path = os.path.join(HERE, "solve_chain7_T200_b%d.npz" % b)
+        if _have(path):
+            continue
+        t0 = time.time()
+        solver, log = ob.solve(W.chain7_batch(B=1024, T=200), b, "reference", maxiter=maxiter)
+        tr = solver_trace(solver, log)
+        tr.pop("Vxx")  # 201 x 28 x 28: three quarters of the file; K, k, Vx, Qu stay
+        tr["maxiter"] = np.array(maxiter)
+        np.savez_compressed(path, **tr)
+        print("solve chain7 T=200", b, "iters", solver.iter, solver.converged, "%.1fs" % (time.time() - t0))
 
 
 if __name__ == "__main__":

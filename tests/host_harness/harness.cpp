@@ -34,8 +34,7 @@ extern "C" int hh_knot_eval(const AslrProblemDesc* desc, int terminal, int diff,
     return vsa ? run<N, 2 * N, true>(desc, terminal, diff, x, u, Kocp, mref, xnext, cost, rec, xout, dFx, dFu) \
                : run<N, N, false>(desc, terminal, diff, x, u, Kocp, mref, xnext, cost, rec, xout, dFx, dFu);   \
   }
-  CASE(2)
-  CASE(7)
+  CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7)
 #undef CASE
   return -1;
 }
@@ -98,8 +97,10 @@ extern "C" int hh_solve(const AslrProblemDesc* desc, const AslrBatch* batch, con
                         const AslrSolverBuffers* buf, int* iters_out) {
   const int n = desc->robot.n;
   const bool vsa = desc->dyn.kind == ASLR_DYN_VSA;
-  if (n == 2) return vsa ? solve_t<2, true>(desc, batch, opts, buf, iters_out) : solve_t<2, false>(desc, batch, opts, buf, iters_out);
-  if (n == 7) return vsa ? solve_t<7, true>(desc, batch, opts, buf, iters_out) : solve_t<7, false>(desc, batch, opts, buf, iters_out);
+#define CASE(N) \
+  if (n == N) return vsa ? solve_t<N, true>(desc, batch, opts, buf, iters_out) : solve_t<N, false>(desc, batch, opts, buf, iters_out);
+  CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7)
+#undef CASE
   return -1;
 }
 
@@ -116,7 +117,26 @@ extern "C" int hh_quasi_static(const AslrProblemDesc* desc, const double* x, con
                                double* u) {
   const int n = desc->robot.n;
   const bool vsa = desc->dyn.kind == ASLR_DYN_VSA;
-  if (n == 2) return vsa ? qs_t<2, true>(desc, x, Kocp, maxiter, tol, u) : qs_t<2, false>(desc, x, Kocp, maxiter, tol, u);
-  if (n == 7) return vsa ? qs_t<7, true>(desc, x, Kocp, maxiter, tol, u) : qs_t<7, false>(desc, x, Kocp, maxiter, tol, u);
+#define CASE(N) \
+  if (n == N) return vsa ? qs_t<N, true>(desc, x, Kocp, maxiter, tol, u) : qs_t<N, false>(desc, x, Kocp, maxiter, tol, u);
+  CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7)
+#undef CASE
   return -1;
+}
+
+// the device-side box QP (backward_dev.cuh: boxqp_solve) on its own, for the brute-force KKT pins of
+// tests/test_solver_pins.py.  H row-major nu x nu; Hinv receives the free-block inverse scattered into nu x nu.
+extern "C" int hh_boxqp(int nu, const double* H, const double* q, const double* lb, const double* ub,
+                        const double* xinit, double* x, double* Hinv, int* clamped) {
+  bool cl[ASLR_MAX_NU];
+  bool ok = false;
+  switch (nu) {
+    case 1: ok = boxqp_solve<1>(H, q, lb, ub, xinit, x, Hinv, cl); break;
+    case 2: ok = boxqp_solve<2>(H, q, lb, ub, xinit, x, Hinv, cl); break;
+    case 3: ok = boxqp_solve<3>(H, q, lb, ub, xinit, x, Hinv, cl); break;
+    case 4: ok = boxqp_solve<4>(H, q, lb, ub, xinit, x, Hinv, cl); break;
+    default: return -1;
+  }
+  for (int i = 0; i < nu; ++i) clamped[i] = cl[i] ? 1 : 0;
+  return ok ? 0 : 1;
 }

@@ -20,7 +20,8 @@ import pinocchio  # noqa: E402
 from oracle import aslr_port as port  # noqa: E402
 
 _PORT_KIND = {"placement": port.FRAME_PLACEMENT, "state": port.STATE, "control": port.CONTROL,
-              "stiffness": port.STIFFNESS, "pendulum": port.DOUBLE_PENDULUM}
+              "stiffness": port.STIFFNESS, "pendulum": port.DOUBLE_PENDULUM,
+              "pendulum_residual": port.RESIDUAL_DOUBLE_PENDULUM}
 SOLVERS = {"ddp": crocoddyl.SolverDDP, "fddp": crocoddyl.SolverFDDP, "boxddp": crocoddyl.SolverBoxDDP}
 
 
@@ -101,6 +102,9 @@ def reference_models(w, b=0):
                 c = aslr_to.CostModelStiffness(state, nu, t["act"][0], t["ref"])
             elif t["kind"] == "pendulum":
                 c = aslr_to.CostModelDoublePendulum(state, crocoddyl.ActivationModelWeightedQuad(t["act"]), nu)
+            elif t["kind"] == "pendulum_residual":
+                c = crocoddyl.CostModelResidual(state, crocoddyl.ActivationModelWeightedQuad(t["act"]),
+                                                aslr_to.ResidualModelDoublePendulum(state, nu))
             cs.addCost(t["name"], c, t["weight"])
         return cs
 

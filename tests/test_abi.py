@@ -38,9 +38,10 @@ def test_library_exports_every_declared_symbol(built_library):
 def test_struct_sizes_match_the_c_header(built_library, tmp_path):
     """Compile a tiny C program against the header and compare sizeof() with ctypes."""
     names = ["AslrSE3", "AslrJoint", "AslrRobot", "AslrDynamics", "AslrCostTerm", "AslrCostSum", "AslrProblemDesc",
-             "AslrBatch", "AslrKnotOut", "AslrSolverOpts", "AslrOcpState", "AslrSolverBuffers", "AslrSolveResult"]
+             "AslrBatch", "AslrKnotOut", "AslrSolverOpts", "AslrOcpState", "AslrSolverBuffers", "AslrSolveResult",
+             "AslrHostSolveIO"]
     mirror = [A.SE3, A.Joint, A.Robot, A.Dynamics, A.CostTerm, A.CostSum, A.ProblemDesc, A.Batch, A.KnotOut,
-              A.SolverOpts, A.OcpState, A.SolverBuffers, A.SolveResult]
+              A.SolverOpts, A.OcpState, A.SolverBuffers, A.SolveResult, A.HostSolveIO]
     src = tmp_path / "sz.c"
     src.write_text('#include <stdio.h>\n#include "aslr_b200.h"\nint main(void){' +
                    "".join('printf("%%zu\\n", sizeof(%s));' % n for n in names) + "return 0;}\n")
@@ -66,10 +67,21 @@ def test_problem_create_validates_without_a_gpu(built_library):
     bad = W.to_desc(W.two_dof_sea())
     bad.running.terms[0].kind = A.COST_STIFFNESS
     assert lib.aslr_problem_create(C.byref(bad), C.byref(h)) == -1
+    # every link DOF 1 .. ASLR_MAX_DOF is instantiated (the reference's classes take any pinModel.nv)
+    for n_dof in range(1, 8):
+        ok = W.to_desc(W.chain_batch(n_dof, B=1, T=2))
+        assert lib.aslr_problem_create(C.byref(ok), C.byref(h)) == 0
+        assert lib.aslr_problem_dims(h, C.byref(n), C.byref(nx), C.byref(nu), C.byref(rec)) == 0
+        assert (n.value, nx.value, nu.value) == (n_dof, 4 * n_dof, n_dof)
+        lib.aslr_problem_destroy(h)
     bad = W.to_desc(W.two_dof_sea())
-    bad.robot.n = 3
-    bad.dyn.nu = 3
-    assert lib.aslr_problem_create(C.byref(bad), C.byref(h)) == -4  # kernels instantiated for n = 2, 7
+    bad.robot.n = 8
+    bad.dyn.nu = 8
+    assert lib.aslr_problem_create(C.byref(bad), C.byref(h)) == -4  # ASLR_ERR_UNSUPPORTED beyond ASLR_MAX_DOF
+    # the residual-model form of the pendulum cost needs two link DOF, like the cost-model form
+    bad = W.to_desc(W.chain_batch(3, B=1, T=2))
+    bad.running.terms[0].kind = A.COST_RESIDUAL_DOUBLE_PENDULUM
+    assert lib.aslr_problem_create(C.byref(bad), C.byref(h)) == -1
 
 
 def test_product_refuses_to_run_without_cuda():

@@ -15,7 +15,8 @@ from util import golden, rel_err
 pin = ob.pinocchio
 croc = ob.crocoddyl
 
-SINGLES = {"double_pendulum": W.double_pendulum, "two_dof_sea": W.two_dof_sea,
+SINGLES = {"double_pendulum": W.double_pendulum, "double_pendulum_residual": W.double_pendulum_residual,
+           "two_dof_sea": W.two_dof_sea,
            "two_dof_vsa_boxddp": W.two_dof_vsa_boxddp, "two_dof_vsa_modified": W.two_dof_vsa_modified}
 KNOT_FIELDS = ("xnext", "cost", "xout", "dFx", "dFu", "Fx", "Fu", "Lx", "Lu", "Lxx", "Lxu", "Luu")
 
@@ -175,8 +176,8 @@ def test_solver_shim_solves_lqr_in_one_iteration(solver_cls):
 
 
 # --------------------------------------------------------------------------------------- the port
-@pytest.mark.parametrize("name", ["double_pendulum", "two_dof_sea", "two_dof_vsa_boxddp", "two_dof_vsa_modified",
-                                  "chain7", "chain7_vsa"])
+@pytest.mark.parametrize("name", ["double_pendulum", "double_pendulum_residual", "two_dof_sea", "two_dof_vsa_boxddp",
+                                  "two_dof_vsa_modified", "chain7", "chain7_vsa"])
 def test_port_matches_golden_knots(name):
     w = all_knot_workloads()[name]
     g = golden("knots_" + name)
@@ -215,7 +216,8 @@ def test_port_solver_trace_matches_golden(name):
 
 
 @pytest.mark.skipif(not ob.refenv.have_reference(), reason="/root/reference only exists in the build container")
-@pytest.mark.parametrize("name", ["double_pendulum", "two_dof_sea", "two_dof_vsa_modified", "chain7"])
+@pytest.mark.parametrize("name", ["double_pendulum", "double_pendulum_residual", "two_dof_sea", "two_dof_vsa_modified",
+                                  "chain7"])
 def test_port_matches_reference_on_fresh_inputs(name):
     w = all_knot_workloads()[name]
     rng = np.random.default_rng(99)

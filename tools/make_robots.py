@@ -102,7 +102,17 @@ def chain7():
     return dict(name="chain7", gravity=[0, 0, -9.81], joints=j, frames=f)
 
 
+def chain_n(n):
+    """The first n joints of chain7 with the tip frame moved to the last kept joint: fixtures for every link
+    DOF the kernels are instantiated for (the reference's classes work for any pinModel.nv,
+    python/aslr_to/statemultibody_aslr.py:14-16)."""
+    c = chain7()
+    tip = c["frames"][-1]
+    f = c["frames"][:n + 1] + [dict(tip, parent=n - 1)]
+    return dict(name="chain%d" % n, gravity=c["gravity"], joints=c["joints"][:n], frames=f)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    for r in (asr_twodof(), double_pendulum(), chain7()):
+    for r in [asr_twodof(), double_pendulum(), chain7()] + [chain_n(n) for n in range(1, 7)]:
         dump(r)
