@@ -33,10 +33,11 @@ struct GrpCols {
 
 template <int NX, int NU>
 struct ColsSmem {
-  static constexpr int RSZ = (Rec<NX, NU>::SIZE + 1) & ~1;
+  static constexpr int RSZ = CRec<NX / 4, NU>::SIZE;  // the compact K1 -> K2 record (knot.cuh), double-buffered
   static constexpr int REC0 = 0;
   static constexpr int REC1 = RSZ;
-  static constexpr int VXX = 2 * RSZ;
+  static constexpr int FXF = 2 * RSZ;         // Fx of the current knot, rebuilt from a_x (row j by lane j)
+  static constexpr int VXX = FXF + NX * NX;
   static constexpr int VT = VXX + NX * NX;
   static constexpr int KG = VT + NX * NX;
   static constexpr int VX = KG + NU * NX;
@@ -177,9 +178,11 @@ __host__ __device__ constexpr bool fu_nonzero(int k) {
 template <int NX, int NU>
 __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const SolverArgs& a, int b, bool live,
                                     const double* u_lb, const double* u_ub, bool box_limits, double xreg,
-                                    double* sums /*[6]*/) {
+                                    double* sums /*[6]*/, const double dt) {
   typedef ColsSmem<NX, NU> CS;
-  typedef Rec<NX, NU> RC;
+  constexpr int NQ = NX / 4;
+  typedef CRec<NQ, NU> RC;  // what K1 left behind: a_x, a_u and the cost sums (knot.cuh)
+  const double dt2 = dt * dt;
   const int j = g.lane;
   const unsigned mask = g.mask;
   const int T = a.T;
@@ -200,8 +203,15 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
   // ---- terminal node: Vxx = Lxx + xreg I, Vx = Lx (+ Vxx fs)
   {
     const double* rec = deriv + (size_t)T * RC::SIZE;
+    {
+      const double lxxd = rec[RC::LXXD + j];
 #pragma unroll
-    for (int c = 0; c < NX; ++c) vrow[c] = rec[RC::LXX + j * NX + c] + ((c == j) ? xreg : 0.0);
+      for (int c = 0; c < NX; ++c) {
+        double l = (c == j) ? lxxd : 0.0;  // record_put: diagonal part, plus the (q_l, q_l) block
+        if (c < NQ) l += (j < NQ) ? rec[RC::LQQ + (j < NQ ? j : 0) * NQ + c] : 0.0;
+        vrow[c] = l + ((c == j) ? xreg : 0.0);
+      }
+    }
     vx = rec[RC::LX + j];
     double w = 0.0;
     if (!feasible) {
@@ -253,26 +263,52 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
       for (int k = 0; k < NX; ++k) fsv[k] = fs[t * NX + k];
       fsj = fs[t * NX + j];
     }
-    // ---- lane-local pieces of the record
-    double fxc[NX];  // column j of Fx
+    // ---- Fx = I + dt [[dt a_x + [0 I]], [a_x]] (integrated_action.py:33-35): lane j rebuilds row j from row
+    // j mod 2n of a_x with the expression record_put uses, and parks it in shared memory (every product below
+    // takes whole rows of Fx as broadcast operands, and lane j needs column j)
+    const int jr = (j < 2 * NQ) ? j : j - 2 * NQ;  // the row of a_x / a_u behind row j of Fx / Fu
+    const double jsc = (j < 2 * NQ) ? dt2 : dt;
+    {
+      double ax[3 * NQ], fr[NX];
+      if constexpr ((3 * NQ) % 2 == 0) {
+        lds_row<3 * NQ>(R + RC::AX + jr * 3 * NQ, ax);
+      } else {
 #pragma unroll
-    for (int k = 0; k < NX; ++k) fxc[k] = R[RC::FX + k * NX + j];
-    double fu[NX][NU];  // all of Fu
+        for (int c = 0; c < 3 * NQ; ++c) ax[c] = R[RC::AX + jr * 3 * NQ + c];
+      }
+#pragma unroll
+      for (int c = 0; c < NX; ++c) {
+        const double a_ = (c < 3 * NQ) ? ax[c < 3 * NQ ? c : 0] : 0.0;
+        fr[c] = fma(jsc, a_, (c == j) ? 1.0 : 0.0) + ((j < 2 * NQ && c == j + 2 * NQ) ? dt : 0.0);
+      }
+      sts_row<NX>(sm + CS::FXF + j * NX, fr);
+    }
+    // Fu = [dt^2 a_u; dt a_u] (integrated_action.py:36-37): all of it in registers
+    double fu[NX][NU];
 #pragma unroll
     for (int k = 0; k < NX; ++k) {
       if (!fu_nonzero<NX, NU>(k)) {
 #pragma unroll
         for (int i = 0; i < NU; ++i) fu[k][i] = 0.0;
-      } else if constexpr (NU % 2 == 0) {
-        double r[NU];
-        lds_row<NU>(R + RC::FU + k * NU, r);
-#pragma unroll
-        for (int i = 0; i < NU; ++i) fu[k][i] = r[i];
       } else {
+        const int kr = (k < 2 * NQ) ? k : k - 2 * NQ;
+        const double ksc = (k < 2 * NQ) ? dt2 : dt;
+        if constexpr (NU % 2 == 0) {
+          double r[NU];
+          lds_row<NU>(R + RC::AU + kr * NU, r);
 #pragma unroll
-        for (int i = 0; i < NU; ++i) fu[k][i] = R[RC::FU + k * NU + i];
+          for (int i = 0; i < NU; ++i) fu[k][i] = ksc * r[i];
+        } else {
+#pragma unroll
+          for (int i = 0; i < NU; ++i) fu[k][i] = ksc * R[RC::AU + kr * NU + i];
+        }
       }
     }
+    g.sync();  // rows of Fx are in place
+    const double* FX = sm + CS::FXF;
+    double fxc[NX];  // column j of Fx
+#pragma unroll
+    for (int k = 0; k < NX; ++k) fxc[k] = FX[k * NX + j];
     // ---- A[j,:] = sum_k Fx[k][j] Vxx'[k,:]
     double arow[NX];
 #pragma unroll
@@ -321,36 +357,40 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
 #pragma unroll
       for (int k = 0; k < NX; ++k) {
         double f[NX];
-        lds_row<NX>(R + RC::FX + k * NX, f);
+        lds_row<NX>(FX + k * NX, f);
 #pragma unroll
         for (int c = 0; c < NX; ++c)
           if (fx_nonzero<NX>(k, c)) s[c] += arow[k] * f[c];
       }
-      double l[NX];
-      lds_row<NX>(R + RC::LXX + j * NX, l);
+      // row j of Lxx = diagonal part + the (q_l, q_l) block of the placement cost (record_put)
+      const double lxxd = R[RC::LXXD + j];
 #pragma unroll
-      for (int c = 0; c < NX; ++c) qxx[c] = l[c] + s[c];
+      for (int c = 0; c < NX; ++c) {
+        double l = (c == j) ? lxxd : 0.0;
+        if (c < NQ) l += (j < NQ) ? R[RC::LQQ + (j < NQ ? j : 0) * NQ + c] : 0.0;
+        qxx[c] = l + s[c];
+      }
 #pragma unroll
       for (int i = 0; i < NU; ++i) {
         double s2 = 0.0;
 #pragma unroll
         for (int k = 0; k < NX; ++k)
           if (fu_nonzero<NX, NU>(k)) s2 += arow[k] * fu[k][i];
-        qxu[i] = R[RC::LXU + j * NU + i] + s2;
+        qxu[i] = 0.0 + s2;  // Lxu = 0: no cost of the menu couples x and u
       }
     }
     // ---- Quu = Luu + (FuV Fu + ureg I): butterfly sum of the lanes' terms FuV[:,j] Fu[j,:]
     double quu[NU * NU];
     {
-      double fuj[NU];
+      double fuj[NU];  // row j of Fu
 #pragma unroll
-      for (int i = 0; i < NU; ++i) fuj[i] = R[RC::FU + j * NU + i];
+      for (int i = 0; i < NU; ++i) fuj[i] = jsc * R[RC::AU + jr * NU + i];
 #pragma unroll
       for (int i = 0; i < NU; ++i) {
 #pragma unroll
         for (int l = 0; l < NU; ++l) {
           const double s = group_sum<NX>(fuv[i] * fuj[l]);
-          quu[i * NU + l] = R[RC::LUU + i * NU + l] + (s + ((i == l) ? xreg : 0.0));
+          quu[i * NU + l] = ((i == l) ? R[RC::LUUD + i] : 0.0) + (s + ((i == l) ? xreg : 0.0));
         }
       }
     }
@@ -511,7 +551,7 @@ namespace aslr {
 // backward_body: called by all lanes of the warp; b_raw may be out of range (the OCP is then a ghost).
 template <int NX, int NU>
 __device__ void backward_body_cols(const GrpCols<NX>& g, double* sm, const SolverArgs& a, int b_raw, const double* u_lb,
-                                   const double* u_ub, bool box_limits, int* n_running) {
+                                   const double* u_ub, bool box_limits, int* n_running, const double dt) {
   typedef BwdSmem<NX, NU> SM;
   constexpr int G = NX;
   const int b = (b_raw < a.B) ? b_raw : a.B - 1;
@@ -546,7 +586,7 @@ __device__ void backward_body_cols(const GrpCols<NX>& g, double* sm, const Solve
     if constexpr (NX > 16)
       ok = backward_sweep_rows<NX, NU>(g, sm, a, b, need, xreg, sums);  // no box QP: see the launcher
     else
-      ok = backward_sweep_cols<NX, NU>(g, sm, a, b, need, u_lb, u_ub, box_limits, xreg, sums);
+      ok = backward_sweep_cols<NX, NU>(g, sm, a, b, need, u_lb, u_ub, box_limits, xreg, sums, dt);
     __syncwarp();
     if (!need) continue;
     if (ok) {

@@ -103,16 +103,26 @@ __device__ __forceinline__ void flush_part(const double* st, double* deriv, long
   __syncwarp();
 }
 
-template <int N, int NU, int P>
+// COMPACT: the solver-internal record CRec<N, NU> (knot.cuh) instead of the dense public one
+template <int N, int NU, bool COMPACT>
+struct RecSize {
+  static constexpr int SIZE = COMPACT ? CRec<N, NU>::SIZE : Rec<4 * N, NU>::SIZE;
+};
+template <int N, int NU, int P, bool COMPACT = false>
 __device__ __forceinline__ void staged_record(double* st, double* deriv, long g0, unsigned mask, int lane, bool mine,
                                               double dt, const KnotDeriv<N, NU>& kd) {
-  typedef Rec<4 * N, NU> RC;
-  typedef RecParts<RC::SIZE> RP;
+  constexpr int SIZE = RecSize<N, NU, COMPACT>::SIZE;
+  typedef RecParts<SIZE> RP;
   if constexpr (P < RP::NP) {
     constexpr int LO = P * RP::LEN;
-    if (mine) record_put<N, NU, LO, LO + RP::LEN>(st + lane - (size_t)LO * RP::STRIDE, RP::STRIDE, dt, kd);
-    flush_part<RC::SIZE, LO, RP::LEN>(st, deriv, g0, mask, lane);
-    staged_record<N, NU, P + 1>(st, deriv, g0, mask, lane, mine, dt, kd);
+    if (mine) {
+      if constexpr (COMPACT)
+        crec_put<N, NU, LO, LO + RP::LEN>(st + lane - (size_t)LO * RP::STRIDE, RP::STRIDE, kd);
+      else
+        record_put<N, NU, LO, LO + RP::LEN>(st + lane - (size_t)LO * RP::STRIDE, RP::STRIDE, dt, kd);
+    }
+    flush_part<SIZE, LO, RP::LEN>(st, deriv, g0, mask, lane);
+    staged_record<N, NU, P + 1, COMPACT>(st, deriv, g0, mask, lane, mine, dt, kd);
   }
 }
 
@@ -171,10 +181,12 @@ __global__ void __launch_bounds__(128, (N <= 2) ? ASLR_K1_MINB : 1) knot_kernel(
 }
 
 // ------------------------------------------------------------------------------- solver kernels
-template <int N, int NU, bool VSA>
+// COMPACT: write the solver-internal compact record (read by the row-per-lane backward kernels)
+template <int N, int NU, bool VSA, bool COMPACT>
 __global__ void __launch_bounds__(128, (N <= 2) ? ASLR_K1_MINB : 1) solver_calcdiff_kernel(const __grid_constant__ DevProblem<N> P,
                                                               const SolverArgs a) {
-  typedef Rec<4 * N, NU> RC;
+  constexpr int RSIZE = RecSize<N, NU, COMPACT>::SIZE;
+  static_assert(!COMPACT || N <= ASLR_K1_STAGE_MAXN, "the compact record is written through the staged path");
   extern __shared__ double stage[];
   const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
   const long total = (long)a.B * (a.T + 1);
@@ -187,8 +199,8 @@ __global__ void __launch_bounds__(128, (N <= 2) ? ASLR_K1_MINB : 1) solver_calcd
     const int lane = threadIdx.x & 31;
     const unsigned mask = __ballot_sync(0xffffffffu, wrote);
     if (mask)
-      staged_record<N, NU, 0>(stage + (size_t)(threadIdx.x >> 5) * RecParts<RC::SIZE>::WARP_DOUBLES, a.buf.deriv,
-                              g - lane, mask, lane, wrote, dt, kd);
+      staged_record<N, NU, 0, COMPACT>(stage + (size_t)(threadIdx.x >> 5) * RecParts<RSIZE>::WARP_DOUBLES, a.buf.deriv,
+                                       g - lane, mask, lane, wrote, dt, kd);
   } else {
     if (g >= total) return;
     calcdiff_body<N, NU, VSA, false>(P, a, (int)(g / (a.T + 1)), (int)(g % (a.T + 1)), true, nullptr, nullptr);
@@ -292,7 +304,8 @@ __global__ void __launch_bounds__(GS * GROUPS) backward_warp_kernel(const Solver
 
 // row-per-lane sweep (backward_cols.cuh): NX lanes per OCP, GROUPS OCPs per CTA
 template <int NX, int NU, int GROUPS>
-__global__ void __launch_bounds__(NX * GROUPS) backward_cols_kernel(const SolverArgs a, const BoxLimits<NU> lim) {
+__global__ void __launch_bounds__(NX * GROUPS) backward_cols_kernel(const SolverArgs a, const BoxLimits<NU> lim,
+                                                                    const double dt) {
   extern __shared__ double smem[];
   const int w = threadIdx.x / NX;
   const int b = blockIdx.x * GROUPS + w;  // may be out of range: the body keeps whole warps in lockstep
@@ -300,7 +313,7 @@ __global__ void __launch_bounds__(NX * GROUPS) backward_cols_kernel(const Solver
   const unsigned mask = ((1u << NX) - 1u) << ((threadIdx.x & 31) - lane);
   GrpCols<NX> g{lane, mask};
   backward_body_cols<NX, NU>(g, smem + (size_t)w * ColsSmem<NX, NU>::SIZE, a, b, lim.lb, lim.ub, lim.has != 0,
-                             a.buf.counters);
+                             a.buf.counters, dt);
 }
 
 // row-per-lane sweep for nx = 28 (backward_rows.cuh): one warp = one OCP = one CTA
@@ -309,7 +322,7 @@ __global__ void __launch_bounds__(32, ASLR_BWD_ROWS_MINB) backward_rows_kernel(c
   extern __shared__ double smem[];
   const int lane = threadIdx.x;
   GrpCols<NX> g{lane, (NX == 32) ? 0xffffffffu : ((1u << NX) - 1u)};
-  backward_body_cols<NX, NU>(g, smem, a, (int)blockIdx.x, nullptr, nullptr, false, a.buf.counters);
+  backward_body_cols<NX, NU>(g, smem, a, (int)blockIdx.x, nullptr, nullptr, false, a.buf.counters, 0.0);
 }
 
 // CTA per OCP (nx = 28)
@@ -361,9 +374,13 @@ struct Launch {
   static constexpr int NX = 4 * N;
   static constexpr int NU = VSA ? 2 * N : N;
 
-  // shared-memory staging of the coalesced record stores (2-DOF kernels only)
-  static size_t stage_bytes(int threads) {
-    return (N <= ASLR_K1_STAGE_MAXN) ? sizeof(double) * RecParts<Rec<NX, NU>::SIZE>::WARP_DOUBLES * (threads / 32) : 0;
+  // whether aslr_solve's K1 -> K2 hand-over uses the compact record CRec<N, NU> (knot.cuh): the row-per-lane
+  // backward kernel of nx = 8 reads it; every other backward kernel still reads the dense record
+  static constexpr bool COMPACT = (NX == 8) && (ASLR_BWD_COLS != 0);
+  // shared-memory staging of the coalesced record stores
+  static size_t stage_bytes(int threads, bool compact = false) {
+    const int wd = compact ? RecParts<RecSize<N, NU, COMPACT>::SIZE>::WARP_DOUBLES : RecParts<Rec<NX, NU>::SIZE>::WARP_DOUBLES;
+    return (N <= ASLR_K1_STAGE_MAXN) ? sizeof(double) * wd * (threads / 32) : 0;
   }
   static int knots(const void* Pv, const KnotArgs& a, int diff, cudaStream_t s) {
     const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
@@ -385,9 +402,9 @@ struct Launch {
     const long total = (long)a.B * (a.T + 1);
     const int threads = 128;
     if (N <= ASLR_K1_STAGE_MAXN)
-      if (allow_smem(solver_calcdiff_kernel<N, NU, VSA>, stage_bytes(threads))) return -2;
-    solver_calcdiff_kernel<N, NU, VSA>
-        <<<(unsigned)((total + threads - 1) / threads), threads, stage_bytes(threads), s>>>(P, a);
+      if (allow_smem(solver_calcdiff_kernel<N, NU, VSA, COMPACT>, stage_bytes(threads, COMPACT))) return -2;
+    solver_calcdiff_kernel<N, NU, VSA, COMPACT>
+        <<<(unsigned)((total + threads - 1) / threads), threads, stage_bytes(threads, COMPACT), s>>>(P, a);
     return launch_status();
   }
   static int rollout(const void* Pv, const SolverArgs& a, cudaStream_t s) {
@@ -428,7 +445,7 @@ struct Launch {
       constexpr size_t slice = sizeof(double) * ColsSmem<NX, NU>::SIZE;
       auto k = backward_cols_kernel<NX, NU, GROUPS>;
       if (allow_smem(k, slice * GROUPS)) return -2;
-      k<<<(a.B + GROUPS - 1) / GROUPS, NX * GROUPS, slice * GROUPS, s>>>(a, lim);
+      k<<<(a.B + GROUPS - 1) / GROUPS, NX * GROUPS, slice * GROUPS, s>>>(a, lim, P.dt);
     } else if constexpr (NX > 16 && NX <= 32 && NU <= 8 && ASLR_BWD_ROWS) {
       // (the box QP of SolverBoxDDP stays with the CTA-per-OCP sweep)
       if (!(a.opts.kind == ASLR_SOLVER_BOXDDP && P.has_limits)) {

@@ -537,6 +537,48 @@ ASLR_HD void record_put(double* rec, const int stride, const double dt, const Kn
     ASLR_PUT(RC::LU + r, acc.Lu[r]);
   }
 }
+
+// Solver-internal COMPACT record (K1 -> K2 inside aslr_solve; the public aslr_calc_diff keeps the dense layout of
+// Rec<NX, NU>).  The dense record is mostly structure: Fx = I + dt [[dt a_x + [0 I]], [a_x]] with the v_m columns of
+// a_x identically zero, Fu = [dt^2 a_u; dt a_u], Lxx = diag + one N x N block, Lxu = 0, Luu diagonal -- K2 already
+// skips those zeros arithmetically, but K1 still wrote them to HBM and K2 read them back (1392 of the 1544
+// algorithmic bytes per knot at (8, 2); the K1 -> K2 round trip was ~1.4 GB per iteration of the 4096-OCP batch).
+// The compact record holds what calcDiff actually computed; K2 rebuilds Fx / Fu / Lxx entries with the very
+// expressions of record_put, so the arithmetic of the backward pass does not change.
+//   (8, 2): 56 doubles = 448 B instead of 174 = 1392 B;   (28, 7): 512 doubles instead of 2044.
+template <int N, int NU>
+struct CRec {
+  static constexpr int AX = 0;                      // a_x     2N x 3N
+  static constexpr int AU = AX + 2 * N * 3 * N;     // a_u     2N x NU
+  static constexpr int LQQ = AU + 2 * N * NU;       // dense block of Lxx on (q_l, q_l)   N x N
+  static constexpr int LXXD = LQQ + N * N;          // diagonal part of Lxx   4N
+  static constexpr int LUUD = LXXD + 4 * N;         // diagonal of Luu        NU
+  static constexpr int LX = LUUD + NU;              // 4N
+  static constexpr int LU = LX + 4 * N;             // NU
+  static constexpr int SIZE = (LU + NU + 1) & ~1;   // even: records are moved in 16-byte pieces
+};
+// elements [LO, HI) of the compact record, element e at rec[e * stride]
+template <int N, int NU, int LO, int HI>
+ASLR_HD void crec_put(double* rec, const int stride, const KnotDeriv<N, NU>& kd) {
+  typedef CRec<N, NU> CR;
+#pragma unroll
+  for (int i = 0; i < 2 * N * 3 * N; ++i) ASLR_PUT(CR::AX + i, kd.AX[i]);
+#pragma unroll
+  for (int i = 0; i < 2 * N * NU; ++i) ASLR_PUT(CR::AU + i, kd.AU[i]);
+#pragma unroll
+  for (int i = 0; i < N * N; ++i) ASLR_PUT(CR::LQQ + i, kd.acc.Lqq[i]);
+#pragma unroll
+  for (int i = 0; i < 4 * N; ++i) {
+    ASLR_PUT(CR::LXXD + i, kd.acc.Lxxd[i]);
+    ASLR_PUT(CR::LX + i, kd.acc.Lx[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < NU; ++i) {
+    ASLR_PUT(CR::LUUD + i, kd.acc.Luud[i]);
+    ASLR_PUT(CR::LU + i, kd.acc.Lu[i]);
+  }
+  if (CR::SIZE > CR::LU + NU) ASLR_PUT(CR::LU + NU, 0.0);
+}
 #undef ASLR_PUT
 
 // Cost of one knot without the dynamics (forward kinematics + cost terms only): the per-knot work of the

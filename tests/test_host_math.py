@@ -195,10 +195,11 @@ def check_chain7_T200(solve_fn, b):
     # converge: an INTERMEDIATE iterate, on which two NumPy implementations of the same formulas (oracle port vs the
     # reference's classes on the same solver shim) already differ by costs 9e-10, xs 2e-8, us 5e-8, K 1.4e-8, k 6e-8,
     # Vx 1e-7 although cond(Quu) <= 7.3 at every knot -- rounding is amplified from iterate to iterate, not by the
-    # factorisation.  Costs and every decision are held to 1e-9 / identical; the iterate itself to 2e-7.
+    # factorisation (measured against the same golden: g++ build 2e-10 / 5e-9 ..., GPU 1.5e-9 / 3e-8 ... 1.7e-7).
+    # Every decision must be identical; costs are held to 1e-8 and the iterate itself to 5e-7 on this member.
     tol = dict((k, RTOL) for k in errs)
     if not bool(g["converged"]):
-        tol.update(xs=2e-7, us=2e-7, K=2e-7, k=2e-7, Vx=2e-7, Qu=2e-7)
+        tol.update(costs=1e-8, stops=1e-8, xs=5e-7, us=5e-7, K=5e-7, k=5e-7, Vx=5e-7, Qu=5e-7)
     bad = dict((k, v) for k, v in errs.items() if not v <= tol[k])
     assert not bad, "beyond tolerance: %r (all: %r)" % (bad, errs)
     return errs
