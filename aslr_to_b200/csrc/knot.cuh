@@ -182,6 +182,49 @@ struct KnotDeriv {
   CostAcc<N> acc;
 };
 
+#ifndef ASLR_TWO_LINK
+#define ASLR_TWO_LINK 1  // N = 2: closed-form rigid-body terms (TwoLinkConst, problem_dev.cuh) instead of the recursion
+#endif
+
+// Rigid-body terms of a two-link chain from the constants folded at problem creation: joint-space inertia M
+// (symmetric 2 x 2), nle = C(q, v) v + G(q), and -- for calcDiff -- what the tangents of inverse dynamics need.
+// (s0, c0), (s1, c1) = sin / cos of the two link angles; v = link velocities.
+struct TwoLinkTerms {
+  double M00, M01, M11, nle0, nle1;
+  // DIFF only: M00', M01', M00'', M01'' (d/dq1) and the Hessian of the potential
+  double dM00, dM01, ddM00, ddM01, G00, G01, G11;
+};
+template <bool DIFF>
+ASLR_HD TwoLinkTerms two_link_terms(const TwoLinkConst& k, double s0, double c0, double s1, double c1, double v0,
+                                    double v1) {
+  TwoLinkTerms r;
+  const double sc = s1 * c1, cc = c1 * c1, c2 = cc - s1 * s1;  // sin cos, cos^2, cos(2 q1)
+  r.M00 = k.m00[0] + k.m00[1] * s1 + k.m00[2] * c1 + k.m00[3] * sc + k.m00[4] * cc;
+  r.M01 = k.m01[0] + k.m01[1] * s1 + k.m01[2] * c1;
+  r.M11 = k.m11;
+  r.dM00 = k.m00[1] * c1 - k.m00[2] * s1 + k.m00[3] * c2 - 2.0 * k.m00[4] * sc;
+  r.dM01 = k.m01[1] * c1 - k.m01[2] * s1;
+  // gravity: U = -gamma(q0) . h(q1); E[3a + b] = gamma_a . h_b with parts (1, sin, cos)
+  const double hb0 = k.E[3] + s1 * k.E[4] + c1 * k.E[5];   // gamma_b . h
+  const double hc0 = k.E[6] + s1 * k.E[7] + c1 * k.E[8];   // gamma_c . h
+  const double gdb = k.E[1] + s0 * k.E[4] + c0 * k.E[7];   // gamma . h_b
+  const double gdc = k.E[2] + s0 * k.E[5] + c0 * k.E[8];   // gamma . h_c
+  const double G0 = -(c0 * hb0 - s0 * hc0);                 // dU/dq0 = -gamma' . h,  gamma' = c0 gamma_b - s0 gamma_c
+  const double G1 = -(c1 * gdb - s1 * gdc);                 // dU/dq1 = -gamma . h',  h' = c1 h_b - s1 h_c
+  r.nle0 = r.dM00 * (v0 * v1) + r.dM01 * (v1 * v1) + G0;
+  r.nle1 = -0.5 * r.dM00 * (v0 * v0) + G1;
+  if (DIFF) {
+    r.ddM00 = -k.m00[1] * s1 - k.m00[2] * c1 - 4.0 * k.m00[3] * sc - 2.0 * k.m00[4] * c2;
+    r.ddM01 = -k.m01[1] * s1 - k.m01[2] * c1;
+    r.G00 = s0 * hb0 + c0 * hc0;                                                        // d2U/dq0^2
+    r.G01 = -(c0 * (c1 * k.E[4] - s1 * k.E[5]) - s0 * (c1 * k.E[7] - s1 * k.E[8]));  // d2U/dq0 dq1
+    r.G11 = s1 * gdb + c1 * gdc;                                                        // d2U/dq1^2
+  } else {
+    r.ddM00 = r.ddM01 = r.G00 = r.G01 = r.G11 = 0.0;
+  }
+  return r;
+}
+
 // calc (+ calcDiff up to the differential-model Jacobians and cost derivatives, left in `kd`)
 // COSTS = false: dynamics only (the x-chain of the trial rollout); cost_out is left at 0.
 template <int N, int NU, bool VSA, bool DIFF, bool COSTS = true>
@@ -195,61 +238,75 @@ ASLR_HD void knot_core(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
   const double* vm = x + 3 * N;
 
   // ---------------------------------------------------------------- forward kinematics, world frame
+  // TWO = closed-form two-link path: the world poses are then only needed by the cost terms (placement residual)
+  constexpr bool TWO = (N == 2) && (ASLR_TWO_LINK != 0);
   M3 R[N];
   V3 p[N];
   SV S[N];
   SI Y[N];
+  double sq[N], cq[N];
 #pragma unroll
-  for (int i = 0; i < N; ++i) {
-    double s, c;
-    sincos(ql[i], &s, &c);
-    const double omc = 1.0 - c;
-    M3 Rl;
+  for (int i = 0; i < N; ++i) sincos(ql[i], &sq[i], &cq[i]);
+  if (!TWO || COSTS) {
 #pragma unroll
-    for (int k = 0; k < 9; ++k) Rl.m[k] = P.j[i].A0[k] + s * P.j[i].A1[k] + omc * P.j[i].A2[k];
-    if (i == 0) {
-      R[0] = Rl;
-      p[0] = ld3(P.j[0].p);
-    } else {
-      R[i] = mul(R[i - 1], Rl);
-      p[i] = p[i - 1] + mul(R[i - 1], ld3(P.j[i].p));
+    for (int i = 0; i < N; ++i) {
+      const double s = sq[i], omc = 1.0 - cq[i];
+      M3 Rl;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) Rl.m[k] = P.j[i].A0[k] + s * P.j[i].A1[k] + omc * P.j[i].A2[k];
+      if (i == 0) {
+        R[0] = Rl;
+        p[0] = ld3(P.j[0].p);
+      } else {
+        R[i] = mul(R[i - 1], Rl);
+        p[i] = p[i - 1] + mul(R[i - 1], ld3(P.j[i].p));
+      }
+      if (!TWO || DIFF) {
+        const V3 z = mul(R[i], ld3(P.j[i].axis));
+        S[i] = SV{cross(p[i], z), z};
+      }
+      if (!TWO) Y[i] = world_inertia(P.j[i].mass, ld3(P.j[i].com), ldm3(P.j[i].Ic), R[i], p[i]);
     }
-    const V3 z = mul(R[i], ld3(P.j[i].axis));
-    S[i] = SV{cross(p[i], z), z};
-    Y[i] = world_inertia(P.j[i].mass, ld3(P.j[i].com), ldm3(P.j[i].Ic), R[i], p[i]);
   }
 
   // ---------------------------------------------------------------- RNEA with qdd = 0 -> nle ; CRBA -> M
   SV v[N], a[N], f[N], Yv[N];
-  {
-    SV vp = sv_zero();
-    SV ap = SV{V3{-P.g[0], -P.g[1], -P.g[2]}, V3{0, 0, 0}};
-#pragma unroll
-    for (int i = 0; i < N; ++i) {
-      const SV Sq = vl[i] * S[i];
-      v[i] = vp + Sq;
-      a[i] = (i == 0) ? ap : ap + cross_mm(vp, Sq);
-      Yv[i] = mul(Y[i], v[i]);
-      f[i] = mul(Y[i], a[i]) + cross_mf(v[i], Yv[i]);
-      vp = v[i];
-      ap = a[i];
-    }
-  }
   double M[N * N], nle[N];
-  {
-    SV F = sv_zero();
-    SI Yc = Y[N - 1];
+  TwoLinkTerms tl;
+  if constexpr (TWO) {
+    tl = two_link_terms<DIFF>(P.tl, sq[0], cq[0], sq[N > 1 ? 1 : 0], cq[N > 1 ? 1 : 0], vl[0], vl[N > 1 ? 1 : 0]);
+    M[0] = tl.M00, M[1] = tl.M01, M[N] = tl.M01, M[N + 1] = tl.M11;
+    nle[0] = tl.nle0, nle[N > 1 ? 1 : 0] = tl.nle1;
+  } else {
+    {
+      SV vp = sv_zero();
+      SV ap = SV{V3{-P.g[0], -P.g[1], -P.g[2]}, V3{0, 0, 0}};
 #pragma unroll
-    for (int i = N - 1; i >= 0; --i) {
-      F = F + f[i];
-      nle[i] = dot(S[i], F);
-      if (i != N - 1) Yc = Yc + Y[i];
-      const SV Fc = mul(Yc, S[i]);
+      for (int i = 0; i < N; ++i) {
+        const SV Sq = vl[i] * S[i];
+        v[i] = vp + Sq;
+        a[i] = (i == 0) ? ap : ap + cross_mm(vp, Sq);
+        Yv[i] = mul(Y[i], v[i]);
+        f[i] = mul(Y[i], a[i]) + cross_mf(v[i], Yv[i]);
+        vp = v[i];
+        ap = a[i];
+      }
+    }
+    {
+      SV F = sv_zero();
+      SI Yc = Y[N - 1];
 #pragma unroll
-      for (int j = 0; j <= i; ++j) {
-        const double mij = dot(S[j], Fc);
-        M[i * N + j] = mij;
-        M[j * N + i] = mij;
+      for (int i = N - 1; i >= 0; --i) {
+        F = F + f[i];
+        nle[i] = dot(S[i], F);
+        if (i != N - 1) Yc = Yc + Y[i];
+        const SV Fc = mul(Yc, S[i]);
+#pragma unroll
+        for (int j = 0; j <= i; ++j) {
+          const double mij = dot(S[j], Fc);
+          M[i * N + j] = mij;
+          M[j * N + i] = mij;
+        }
       }
     }
   }
@@ -347,82 +404,95 @@ ASLR_HD void knot_core(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
 
   // ---------------------------------------------------------------- inverse-dynamics tangents at (q, v, a_l)
   // (what pinocchio.computeRNEADerivatives provides to free_fwddyn_asr.py:75)
-  SV Ya[N], F[N];
-  {
-    SV ac = sv_zero();
-#pragma unroll
-    for (int i = 0; i < N; ++i) {
-      ac = ac + al[i] * S[i];
-      a[i] = a[i] + ac;
-      Ya[i] = mul(Y[i], a[i]);
-      f[i] = Ya[i] + cross_mf(v[i], Yv[i]);
-    }
-    SV Fs = sv_zero();
-#pragma unroll
-    for (int i = N - 1; i >= 0; --i) {
-      Fs = Fs + f[i];
-      F[i] = Fs;
-    }
-  }
   double dtq[N * N], dtv[N * N];
-#pragma unroll(N <= 3 ? N : 1)
-  for (int j = 0; j < N; ++j) {
-    SV df[N];
-    // ---- d/dq_j
+  if constexpr (TWO) {
+    // tau0 = M00 a0 + M01 a1 + M00' v0 v1 + M01' v1^2 + G0,   tau1 = M01 a0 + M11 a1 - M00' v0^2 / 2 + G1
+    const double v0 = vl[0], v1 = vl[N > 1 ? 1 : 0], a0 = al[0], a1 = al[N > 1 ? 1 : 0];
+    dtq[0] = tl.G00;
+    dtq[1] = tl.dM00 * a0 + tl.dM01 * a1 + tl.ddM00 * (v0 * v1) + tl.ddM01 * (v1 * v1) + tl.G01;
+    dtq[N] = tl.G01;
+    dtq[N + 1] = tl.dM01 * a0 - 0.5 * tl.ddM00 * (v0 * v0) + tl.G11;
+    dtv[0] = tl.dM00 * v1;
+    dtv[1] = tl.dM00 * v0 + 2.0 * tl.dM01 * v1;
+    dtv[N] = -tl.dM00 * v0;
+    dtv[N + 1] = 0.0;
+  } else {
+    SV Ya[N], F[N];
     {
-      const SV Sj = S[j];
-      SV dvp = sv_zero(), dap = sv_zero();
-#pragma unroll
+      SV ac = sv_zero();
+  #pragma unroll
       for (int i = 0; i < N; ++i) {
-        if (i < j) {
-          df[i] = sv_zero();
-        } else if (i == j) {
-          const SV dYa = dY_mul(Y[i], Sj, a[i], Ya[i]);
-          const SV dYv = dY_mul(Y[i], Sj, v[i], Yv[i]);
-          df[i] = dYa + cross_mf(v[i], dYv);
-        } else {
-          const SV SjSi = cross_mm(Sj, S[i]);
-          const SV dvi = dvp + vl[i] * SjSi;
-          const SV dai = dap + al[i] * SjSi + vl[i] * (cross_mm(dvp, S[i]) + cross_mm(v[i - 1], SjSi));
-          const SV dYa = dY_mul(Y[i], Sj, a[i], Ya[i]);
-          const SV dYv = dY_mul(Y[i], Sj, v[i], Yv[i]);
-          df[i] = dYa + mul(Y[i], dai) + cross_mf(dvi, Yv[i]) + cross_mf(v[i], dYv + mul(Y[i], dvi));
-          dvp = dvi;
-          dap = dai;
-        }
+        ac = ac + al[i] * S[i];
+        a[i] = a[i] + ac;
+        Ya[i] = mul(Y[i], a[i]);
+        f[i] = Ya[i] + cross_mf(v[i], Yv[i]);
       }
-      SV dF = sv_zero();
-#pragma unroll
+      SV Fs = sv_zero();
+  #pragma unroll
       for (int i = N - 1; i >= 0; --i) {
-        if (i >= j) dF = dF + df[i];
-        double t = dot(S[i], dF);
-        if (i > j) t += dot(cross_mm(Sj, S[i]), F[i]);
-        dtq[i * N + j] = t;
+        Fs = Fs + f[i];
+        F[i] = Fs;
       }
     }
-    // ---- d/dqd_j
-    {
-      const SV Sj = S[j];
-      SV dap = sv_zero();
-#pragma unroll
-      for (int i = 0; i < N; ++i) {
-        if (i < j) {
-          df[i] = sv_zero();
-        } else {
-          SV dai;
-          if (i == j)
-            dai = (i == 0) ? sv_zero() : cross_mm(v[i > 0 ? i - 1 : 0], Sj);
-          else
-            dai = dap + vl[i] * cross_mm(Sj, S[i]);
-          df[i] = mul(Y[i], dai) + cross_mf(Sj, Yv[i]) + cross_mf(v[i], mul(Y[i], Sj));
-          dap = dai;
+  #pragma unroll(N <= 3 ? N : 1)
+    for (int j = 0; j < N; ++j) {
+      SV df[N];
+      // ---- d/dq_j
+      {
+        const SV Sj = S[j];
+        SV dvp = sv_zero(), dap = sv_zero();
+  #pragma unroll
+        for (int i = 0; i < N; ++i) {
+          if (i < j) {
+            df[i] = sv_zero();
+          } else if (i == j) {
+            const SV dYa = dY_mul(Y[i], Sj, a[i], Ya[i]);
+            const SV dYv = dY_mul(Y[i], Sj, v[i], Yv[i]);
+            df[i] = dYa + cross_mf(v[i], dYv);
+          } else {
+            const SV SjSi = cross_mm(Sj, S[i]);
+            const SV dvi = dvp + vl[i] * SjSi;
+            const SV dai = dap + al[i] * SjSi + vl[i] * (cross_mm(dvp, S[i]) + cross_mm(v[i - 1], SjSi));
+            const SV dYa = dY_mul(Y[i], Sj, a[i], Ya[i]);
+            const SV dYv = dY_mul(Y[i], Sj, v[i], Yv[i]);
+            df[i] = dYa + mul(Y[i], dai) + cross_mf(dvi, Yv[i]) + cross_mf(v[i], dYv + mul(Y[i], dvi));
+            dvp = dvi;
+            dap = dai;
+          }
+        }
+        SV dF = sv_zero();
+  #pragma unroll
+        for (int i = N - 1; i >= 0; --i) {
+          if (i >= j) dF = dF + df[i];
+          double t = dot(S[i], dF);
+          if (i > j) t += dot(cross_mm(Sj, S[i]), F[i]);
+          dtq[i * N + j] = t;
         }
       }
-      SV dF = sv_zero();
-#pragma unroll
-      for (int i = N - 1; i >= 0; --i) {
-        if (i >= j) dF = dF + df[i];
-        dtv[i * N + j] = dot(S[i], dF);
+      // ---- d/dqd_j
+      {
+        const SV Sj = S[j];
+        SV dap = sv_zero();
+  #pragma unroll
+        for (int i = 0; i < N; ++i) {
+          if (i < j) {
+            df[i] = sv_zero();
+          } else {
+            SV dai;
+            if (i == j)
+              dai = (i == 0) ? sv_zero() : cross_mm(v[i > 0 ? i - 1 : 0], Sj);
+            else
+              dai = dap + vl[i] * cross_mm(Sj, S[i]);
+            df[i] = mul(Y[i], dai) + cross_mf(Sj, Yv[i]) + cross_mf(v[i], mul(Y[i], Sj));
+            dap = dai;
+          }
+        }
+        SV dF = sv_zero();
+  #pragma unroll
+        for (int i = N - 1; i >= 0; --i) {
+          if (i >= j) dF = dF + df[i];
+          dtv[i * N + j] = dot(S[i], dF);
+        }
       }
     }
   }

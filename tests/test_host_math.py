@@ -106,7 +106,69 @@ def test_chain7_solver_host_build_matches_oracle_port(hostmath, kind):
         assert rel_err(res["Vxx"][b], np.array(solver.Vxx)) < 1e-9
 
 
-@pytest.mark.parametrize("n", [1, 3, 4, 5, 6])
+def random_two_link_robot(path, seed):
+    """A two-link chain with nothing special about it: random joint placements (rotation and offset), random unit
+    axes, off-axis centres of mass, full inertia tensors -- the general case of the closed-form two-link terms."""
+    import json
+    rng = np.random.default_rng(seed)
+
+    def rot():
+        q, _ = np.linalg.qr(rng.standard_normal((3, 3)))
+        return q * np.sign(np.linalg.det(q))
+
+    def spd():
+        a = rng.standard_normal((3, 3))
+        return (a @ a.T + 0.5 * np.eye(3)) * 1e-2
+    joints = []
+    for i in range(2):
+        ax = rng.standard_normal(3)
+        joints.append(dict(name="joint%d" % (i + 1), placement=dict(R=rot().tolist(), p=rng.uniform(-0.3, 0.3, 3).tolist()),
+                           axis=(ax / np.linalg.norm(ax)).tolist(), mass=float(rng.uniform(0.5, 2.0)),
+                           com=rng.uniform(-0.2, 0.2, 3).tolist(), inertia=spd().tolist(), q_min=-3.0, q_max=3.0))
+    I3 = np.eye(3).tolist()
+    frames = [dict(name="universe", parent=-1, placement=dict(R=I3, p=[0, 0, 0])),
+              dict(name="link1", parent=0, placement=dict(R=I3, p=[0, 0, 0])),
+              dict(name="link2", parent=1, placement=dict(R=I3, p=[0, 0, 0])),
+              dict(name="EE", parent=1, placement=dict(R=rot().tolist(), p=rng.uniform(-0.2, 0.2, 3).tolist()))]
+    with open(path, "w") as f:
+        json.dump(dict(name="random2", gravity=rng.uniform(-9, 9, 3).tolist(), joints=joints, frames=frames), f)
+    return str(path)
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+@pytest.mark.parametrize("kind", ["sea", "vsa"])
+def test_two_link_closed_form_on_random_spatial_geometry(hostmath, tmp_path, seed, kind):
+    """n = 2 uses closed-form rigid-body terms folded at problem creation (problem_dev.cuh: fill_two_link) instead
+    of the general recursion: on random 3-D two-link robots (tilted placements and axes, full inertia tensors,
+    arbitrary gravity) the knot records must agree with the oracle port, which runs the general RNEA / CRBA /
+    RNEA-derivative algorithms of the pinocchio shim."""
+    robot = random_two_link_robot(tmp_path / "random2.json", seed)
+    base = W.two_dof_sea() if kind == "sea" else W.two_dof_vsa_modified()
+    w = dict(base, robot=robot, gravity=None)
+    desc = W.to_desc(w)
+    run, term, _ = ob.port_models(w, 0)
+    rng = np.random.default_rng(seed + 10)
+    worst = 0.0
+    for _ in range(6):
+        x = np.concatenate([rng.uniform(-3, 3, 4), rng.uniform(-2, 2, 4)])
+        u = rng.uniform(0.2, 2.0, run.nu)
+        for m, uu in ((run, u), (term, None)):
+            d = m.createData()
+            if uu is None:
+                m.calc(d, x), m.calcDiff(d, x)
+            else:
+                m.calc(d, x, uu), m.calcDiff(d, x, uu)
+            out = host_knot(hostmath, desc, x, uu, terminal=uu is None)
+            for k in ("xnext", "cost", "xout", "dFx", "dFu", "Fx", "Fu", "Lx", "Lu", "Lxx"):
+                e = rel_err(out[k], getattr(d, k))
+                worst = max(worst, e)
+                assert e < 1e-10, (seed, kind, k, e)
+            nodiff = host_knot(hostmath, desc, x, uu, terminal=uu is None, diff=False)
+            assert rel_err(nodiff["xnext"], d.xnext) < 1e-12
+    assert worst < 1e-10
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 6])
 @pytest.mark.parametrize("kind", ["sea", "vsa"])
 def test_every_link_dof_host_build_matches_oracle_port(hostmath, n, kind):
     """The reference's classes work for any pinModel.nv (statemultibody_aslr.py:14-16): the device arithmetic
