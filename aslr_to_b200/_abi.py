@@ -12,6 +12,7 @@ MAX_NU = 2 * MAX_DOF
 MAX_COST_TERMS = 6
 NUM_ALPHAS = 10
 LOG_FIELDS = 8
+COUNTER_INTS = 40
 
 (COST_NONE, COST_FRAME_PLACEMENT, COST_STATE, COST_CONTROL, COST_STIFFNESS, COST_DOUBLE_PENDULUM,
  COST_RESIDUAL_DOUBLE_PENDULUM) = range(7)
@@ -78,11 +79,12 @@ class OcpState(C.Structure):
     _fields_ = [(k, C.c_double) for k in ("cost", "cost_try", "stop", "xreg", "steplength", "dV", "dVexp", "d1", "d2",
                                           "dg", "dq", "ffeas")] + \
                [(k, C.c_int32) for k in ("iter", "status", "is_feasible", "was_feasible", "recalc", "accepted",
-                                         "src_slot", "n_backward_retries", "full_steps", "n_logged")]
+                                         "src_slot", "n_backward_retries", "full_steps", "n_logged", "ls_done",
+                                         "reserved0")]
 
 
 OCP_STATE_DOUBLES = C.sizeof(OcpState) // 8
-assert C.sizeof(OcpState) == 12 * 8 + 10 * 4
+assert C.sizeof(OcpState) == 12 * 8 + 12 * 4
 
 
 class SolverBuffers(C.Structure):

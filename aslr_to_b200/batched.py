@@ -23,7 +23,7 @@ def solver_buffer_shapes(B, T, nx, nu, maxiter, store_vxx=True, store_quu=True, 
         "deriv": (B, T + 1, rec), "fs": (B, T + 1, nx), "Kgain": (B, T, nu, nx), "kff": (B, T, nu),
         "Vx": (B, T + 1, nx), "Vxxfs": (B, T + 1, nx), "Qu": (B, T, nu), "Quuk": (B, T, nu),
         "xs_try": (B, NA, T + 1, nx), "us_try": (B, NA, T, nu), "trial": (B, NA, 4),
-        "state": (B, A.OCP_STATE_DOUBLES), "counters": (2,),  # 4 int32
+        "state": (B, A.OCP_STATE_DOUBLES), "counters": ((A.COUNTER_INTS + 2 * NA * B + 1) // 2,),  # int32: running words + line-search work lists
     }
     if store_vxx:
         shapes["Vxx"] = (B, T + 1, nx, nx)

@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 
 #include "kernels.cuh"
@@ -56,8 +57,8 @@ int launch_accept(const SolverArgs& a, cudaStream_t s) {
 }  // namespace aslr
 
 // aslr_solve splits the batch into sub-batches that run the same kernel sequence on their own streams (see
-// aslr_solve); counters[k] is the "still running" word of sub-batch k (AslrSolverBuffers.counters holds 4 ints)
-#define ASLR_MAX_LANES 4
+// aslr_solve); counters[k] is the "still running" word of sub-batch k (layout of AslrSolverBuffers.counters: make_args)
+#define ASLR_MAX_LANES 8
 #ifndef ASLR_SOLVE_LANES
 #define ASLR_SOLVE_LANES 4
 #endif
@@ -291,6 +292,11 @@ static int make_args(const AslrProblem* p, const AslrBatch* batch, const AslrSol
   a->x0 = batch->x0, a->K_ocp = batch->K_ocp, a->mref_ocp = batch->mref_ocp;
   a->buf = *buf;
   a->opts = *opts;
+  // layout of `counters`: [0, 8) still-running words of the sub-batches, [8, 40) work-list counts and CTA tickets
+  // (four ints per sub-batch), then the work lists, 2 * ASLR_NUM_ALPHAS ints per OCP
+  a->ls_hdr = buf->counters + 8;
+  a->ls_list = buf->counters + ASLR_COUNTER_INTS;
+  a->fuse_accept = 0;
   return ASLR_OK;
 }
 
@@ -360,6 +366,8 @@ static SolverArgs sub_batch(const SolverArgs& a, const AslrProblem* p, int b0, i
   if (q.log) q.log += o * (size_t)a.opts.maxiter * ASLR_LOG_FIELDS;
   q.state += o;
   q.counters += lane;
+  r.ls_hdr = a.ls_hdr + 4 * lane;
+  r.ls_list = a.ls_list + o * 2 * ASLR_NUM_ALPHAS;
   return r;
 }
 
@@ -464,10 +472,10 @@ int aslr_solve(const AslrProblem* pc, const AslrBatch* batch, const AslrSolverOp
       SolverArgs& ak = la[k];
       cudaStream_t sk = ls[k];
       ak.iter = it;
-      if (p->fn.calcdiff(p->dev, ak, sk) || p->fn.backward(p->dev, ak, sk) || p->fn.rollout(p->dev, ak, sk) ||
-          launch_accept(ak, sk))
+      ak.fuse_accept = 1;  // K4 rides on the trial-cost passes (kernels.cuh: linesearch_cost_kernel)
+      if (p->fn.calcdiff(p->dev, ak, sk) || p->fn.backward(p->dev, ak, sk) || p->fn.rollout(p->dev, ak, sk))
         return bail(cudaSuccess);
-      launches += 3 + p->fn.rollout_launches;  // K1, K2, K3 (rollout phases + trial-cost passes), K4
+      launches += 2 + p->fn.rollout_launches;  // K1, K2, K3 (rollout phases + trial-cost / accept passes)
       last_it[k] = it + 1;
       if ((it + 1) % poll == 0 && it + 1 < opts->maxiter) {
         const int slot = n_polls[k] & 1;
@@ -560,7 +568,7 @@ int aslr_solve_host(AslrProblem* p, const AslrHostSolveIO* io, const AslrSolverO
   sz[VX] = B * (T + 1) * nx, sz[VXXFS] = B * (T + 1) * nx, sz[QU] = B * T * nu, sz[QUUK] = B * T * nu;
   sz[XTRY] = B * ASLR_NUM_ALPHAS * (T + 1) * nx, sz[UTRY] = B * ASLR_NUM_ALPHAS * T * nu;
   sz[TRIAL] = B * ASLR_NUM_ALPHAS * 4, sz[LOG] = io->log ? B * mi * ASLR_LOG_FIELDS : 0;
-  sz[STATE] = B * (sizeof(AslrOcpState) / sizeof(double)), sz[CNT] = 2;
+  sz[STATE] = B * (sizeof(AslrOcpState) / sizeof(double)), sz[CNT] = (ASLR_COUNTER_INTS + 2 * ASLR_NUM_ALPHAS * B + 1) / 2;
   sz[X0] = B * nx, sz[KO] = io->K_ocp ? B * n * n : 0, sz[MREF] = io->mref_ocp ? B * 12 : 0;
   size_t off[NSEG], total = 0;
   for (int k = 0; k < NSEG; ++k) off[k] = total, total += (sz[k] + 31) & ~(size_t)31;

@@ -557,6 +557,7 @@ __device__ void backward_body_cols(const GrpCols<NX>& g, double* sm, const Solve
   const int b = (b_raw < a.B) ? b_raw : a.B - 1;
   AslrOcpState& st = a.buf.state[b];
   bool need = (b_raw < a.B) && (st.status == ASLR_OCP_RUNNING);
+  if (b_raw < a.B && !need && g.lane == 0) st.src_slot = -1;  // finished: the adopted slot is history (backward_body)
   if (!__any_sync(ASLR_FULL, need)) return;
   const int T = a.T;
   // ---- cost = sum of knot costs (ShootingProblem::calcDiff), ffeas = max |gap|

@@ -645,7 +645,13 @@ ASLR_HD void backward_body(const Grp& g, double* sm, const SolverArgs& a, int b,
   typedef BwdSmem<NX, NU> SM;
   constexpr int G = Grp::G;
   AslrOcpState& st = a.buf.state[b];
-  if (st.status != ASLR_OCP_RUNNING) return;
+  if (st.status != ASLR_OCP_RUNNING) {
+    // the final candidate was adopted by the calc-diff sweep that ran before us: forget the slot, so the sweeps of
+    // the following iterations do not copy the trajectory again (the fused line search of aslr_solve has no
+    // accept pass over finished OCPs that would do it)
+    if (g.lane == 0) st.src_slot = -1;
+    return;
+  }
   const int T = a.T;
   // ---- cost = sum of knot costs (ShootingProblem::calcDiff), ffeas = max |gap|
   if (st.recalc) {

@@ -219,9 +219,9 @@ __global__ void __launch_bounds__((N <= 2) ? ASLR_ROLL_THREADS : 64, (N <= 2) ? 
   typedef RollStage<4 * N, NU> RS;
   if constexpr (RS::ENABLED && ASLR_ROLL_THREADS == RS::THREADS) {
     __shared__ __align__(16) double stage[RS::CTA_DOUBLES];
-    rollout_body<N, NU, VSA>(P, a, b, ai, stage + threadIdx.x * RS::ROW);
+    rollout_body<N, NU, VSA>(P, a, b, ai, stage + threadIdx.x * RS::ROW, phase);
   } else {
-    rollout_body<N, NU, VSA>(P, a, b, ai);
+    rollout_body<N, NU, VSA>(P, a, b, ai, nullptr, phase);
   }
 }
 
@@ -246,26 +246,58 @@ __global__ void __launch_bounds__(GS * TRIALS, ASLR_ROLLC_MINB) rollout_coop_ker
                                             b, ai);
 }
 
-// K3b: one warp per trial; lanes take the knots 32 at a time, the costs are then added in knot order
-// (shuffle broadcast, every lane keeps the same running total) so the sum equals the sequential one.
+// K3b: costs of the trial trajectories + (in aslr_solve) the line-search decision.  Persistent warps walk the work
+// list of the pass (solver_dev.cuh: ls_append): one warp per trial, lanes take the knots 32 at a time, the costs are
+// then added in knot order (shuffle broadcast, every lane keeps the same running total) so the sum equals the
+// sequential one.  pass 0: alpha = 1 of every running OCP, and whether that full step is taken; pass 1: the other
+// nine step lengths, only for the OCPs whose full step was not taken (lazy line search: the speculative rollouts of
+// an OCP that took alpha = 1 are never costed).  The warp that completes an OCP's line search -- alpha = 1 taken in
+// pass 0, or the ninth trial of pass 1 -- runs accept_body for it (fuse_accept): the decision needs the costs of
+// that OCP and nothing else, so it does not need a kernel of its own.  The last CTA to finish empties the list.
 template <int N, int NU, bool VSA>
-__global__ void __launch_bounds__(128) trial_cost_kernel(const __grid_constant__ DevProblem<N> P, const SolverArgs a,
-                                                         const int pass) {
-  // pass 0: alpha = 1 of every OCP (and its acceptance test); pass 1: the other nine, where still needed
-  const int per = pass == 0 ? 1 : ASLR_NUM_ALPHAS - 1;
-  const long w = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+__global__ void __launch_bounds__(128) linesearch_cost_kernel(const __grid_constant__ DevProblem<N> P, const SolverArgs a,
+                                                              const int pass) {
   const int lane = threadIdx.x & 31;
-  if (w >= (long)a.B * per) return;
-  const int b = (int)(w / per), ai = pass == 0 ? 0 : 1 + (int)(w % per);
-  if (!trial_cost_wanted(a, b, ai)) return;
-  double total = 0.0;
-  for (int base = 0; base <= a.T; base += 32) {
-    const int t = base + lane;
-    const double c = (t <= a.T) ? trial_knot_cost<N, NU, VSA>(P, a, b, ai, t) : 0.0;
-    const int n = (a.T + 1 - base < 32) ? a.T + 1 - base : 32;
-    for (int l = 0; l < n; ++l) total += __shfl_sync(0xffffffffu, c, l);
+  const int warp = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  const int nwarps = (int)((gridDim.x * blockDim.x) >> 5);
+  const int count = a.ls_hdr[pass];
+  const int* list = a.ls_list + (size_t)pass * ASLR_NUM_ALPHAS * a.B;
+  for (int i = warp; i < count; i += nwarps) {
+    const int id = list[i];
+    const int b = id / ASLR_NUM_ALPHAS, ai = id % ASLR_NUM_ALPHAS;
+    double* tr = a.buf.trial + ((size_t)b * ASLR_NUM_ALPHAS + ai) * 4;
+    const double* tr0 = a.buf.trial + (size_t)b * ASLR_NUM_ALPHAS * 4;  // the alpha = 1 record (final since pass 0)
+    if (pass == 1 && tr0[3] != 0.0) continue;  // the full step was taken: this trial was speculation
+    if (tr[2] != 0.0) {  // the rollout did not throw
+      double total = 0.0;
+      for (int base = 0; base <= a.T; base += 32) {
+        const int t = base + lane;
+        const double c = (t <= a.T) ? trial_knot_cost<N, NU, VSA>(P, a, b, ai, t) : 0.0;
+        const int n = (a.T + 1 - base < 32) ? a.T + 1 - base : 32;
+        for (int l = 0; l < n; ++l) total += __shfl_sync(0xffffffffu, c, l);
+      }
+      if (lane == 0) trial_cost_finish(a, b, ai, total);
+    }
+    if (lane == 0 && a.fuse_accept) {
+      AslrOcpState& s = a.buf.state[b];
+      if (pass == 0) {
+        if (tr[3] != 0.0) accept_body(a, b, a.buf.counters);  // full step taken (written by this thread just now)
+      } else {
+        __threadfence();  // this trial's record before the count
+        if (atomicAdd(&s.ls_done, 1) + 1 == ASLR_NUM_ALPHAS - 1) {
+          __threadfence();  // the other trials' records after the count
+          s.ls_done = 0;
+          accept_body(a, b, a.buf.counters);
+        }
+      }
+    }
   }
-  if (lane == 0) trial_cost_finish(a, b, ai, total);
+  // every CTA has read `count` by the time it gets here: the last one to arrive empties the list
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(a.ls_hdr + 2 + pass, 1) == (int)gridDim.x - 1) a.ls_hdr[pass] = 0, a.ls_hdr[2 + pass] = 0;
+  }
 }
 
 // quasiStatic of every running knot: one thread per (OCP, knot)
@@ -407,6 +439,18 @@ struct Launch {
         <<<(unsigned)((total + threads - 1) / threads), threads, stage_bytes(threads, COMPACT), s>>>(P, a);
     return launch_status();
   }
+  // grid of the persistent trial-cost kernel: enough warps for every trial of a small batch, at most three CTAs
+  // per SM (166 registers per thread) otherwise
+  static unsigned cost_blocks(long trials) {
+    static int sms = 0;
+    if (sms == 0) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+    }
+    const long want = (trials + 3) / 4, cap = 3L * sms;
+    return (unsigned)(want < 1 ? 1 : (want < cap ? want : cap));
+  }
   static int rollout(const void* Pv, const SolverArgs& a, cudaStream_t s) {
     const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
     const long total = (long)a.B * ASLR_NUM_ALPHAS;
@@ -417,20 +461,18 @@ struct Launch {
       if (allow_smem(k, bytes)) return -2;
       k<<<(unsigned)((total + TRIALS - 1) / TRIALS), GS * TRIALS, bytes, s>>>(P, a, -1);
       if (launch_status()) return -2;
-      trial_cost_kernel<N, NU, VSA><<<(unsigned)(((long)a.B * 32 + 127) / 128), 128, 0, s>>>(P, a, 0);
-      trial_cost_kernel<N, NU, VSA>
-          <<<(unsigned)(((long)a.B * (ASLR_NUM_ALPHAS - 1) * 32 + 127) / 128), 128, 0, s>>>(P, a, 1);
+      linesearch_cost_kernel<N, NU, VSA><<<cost_blocks(a.B), 128, 0, s>>>(P, a, 0);
+      linesearch_cost_kernel<N, NU, VSA><<<cost_blocks(total - a.B), 128, 0, s>>>(P, a, 1);
       return launch_status();
     } else {
       // two-phase speculative line search (solver_dev.cuh: rollout_wanted)
       const int threads = ASLR_ROLL_THREADS;
       rollout_kernel<N, NU, VSA><<<(unsigned)((total + threads - 1) / threads), threads, 0, s>>>(P, a, 0);
       if (launch_status()) return -2;
-      trial_cost_kernel<N, NU, VSA><<<(unsigned)(((long)a.B * 32 + 127) / 128), 128, 0, s>>>(P, a, 0);
+      linesearch_cost_kernel<N, NU, VSA><<<cost_blocks(a.B), 128, 0, s>>>(P, a, 0);
       rollout_kernel<N, NU, VSA><<<(unsigned)((total - a.B + threads - 1) / threads), threads, 0, s>>>(P, a, 1);
       if (launch_status()) return -2;
-      trial_cost_kernel<N, NU, VSA>
-          <<<(unsigned)(((long)a.B * (ASLR_NUM_ALPHAS - 1) * 32 + 127) / 128), 128, 0, s>>>(P, a, 1);
+      linesearch_cost_kernel<N, NU, VSA><<<cost_blocks(total - a.B), 128, 0, s>>>(P, a, 1);
       return launch_status();
     }
   }

@@ -182,6 +182,9 @@ struct KnotDeriv {
   CostAcc<N> acc;
 };
 
+#ifndef ASLR_TWO_LINK_COFACTOR
+#define ASLR_TWO_LINK_COFACTOR 0  // 1: 2 x 2 inverse by cofactors instead of Cholesky (tuning experiment)
+#endif
 #ifndef ASLR_TWO_LINK
 #define ASLR_TWO_LINK 1  // N = 2: closed-form rigid-body terms (TwoLinkConst, problem_dev.cuh) instead of the recursion
 #endif
@@ -330,12 +333,25 @@ ASLR_HD void knot_core(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
     }
   }
   double L[N * N];
-#pragma unroll
-  for (int i = 0; i < N * N; ++i) L[i] = M[i];
   double Linv[N];
-  cholesky<N>(L, Linv);
-  double al[N], am[N], Minv[DIFF ? N * N : 1];
-  if (DIFF) {
+  constexpr bool COF = TWO && (ASLR_TWO_LINK_COFACTOR != 0);
+  double al[N], am[N], Minv[(DIFF || COF) ? N * N : 1];
+  if constexpr (COF) {
+    // 2 x 2: the inverse by cofactors (one reciprocal instead of a square root and two reciprocals on the chain);
+    // calc and calcDiff share the expression, so the rollout's x' equals the derivative sweep's bit for bit
+    const double idet = 1.0 / (M[0] * M[N + 1] - M[1] * M[1]);
+    Minv[0] = M[N + 1] * idet, Minv[1] = -M[1] * idet, Minv[N] = Minv[1], Minv[N + 1] = M[0] * idet;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      double s = 0;
+#pragma unroll
+      for (int k = 0; k < N; ++k) s += Minv[i * N + k] * (-nle[k] - tauc[k]);
+      al[i] = s;
+    }
+  } else if (DIFF) {
+#pragma unroll
+    for (int i = 0; i < N * N; ++i) L[i] = M[i];
+    cholesky<N>(L, Linv);
     // explicit inverse, as the reference does (free_fwddyn_asr.py:40)
 #pragma unroll
     for (int c = 0; c < N; ++c) {
@@ -354,6 +370,9 @@ ASLR_HD void knot_core(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
       al[i] = s;  // free_fwddyn_asr.py:43 (tau[:n] is zero for every shipped actuation)
     }
   } else {
+#pragma unroll
+    for (int i = 0; i < N * N; ++i) L[i] = M[i];
+    cholesky<N>(L, Linv);
 #pragma unroll
     for (int i = 0; i < N; ++i) al[i] = -nle[i] - tauc[i];
     chol_solve<N>(L, Linv, al);

@@ -337,6 +337,7 @@ ASLR_HD void rollout_coop_body(const Grp& g, double* sm, const double* jc, const
     tr[0] = 0.0;  // filled by the trial-cost pass
     tr[2] = ok ? 1.0 : 0.0;
     tr[3] = 0.0;
+    ls_append(a, b, ai, -1);
   }
 }
 

@@ -16,6 +16,15 @@ struct SolverArgs {
   const double* mref_ocp;
   AslrSolverBuffers buf;
   AslrSolverOpts opts;
+  // Line-search work lists (CUDA kernels only; null in the host emulation).  Every trial that is actually rolled
+  // out appends its id (b * ASLR_NUM_ALPHAS + ai) to list 0 (alpha = 1) or list 1 (the other step lengths), so the
+  // trial-cost passes walk exactly the trials that exist instead of launching a warp per possible trial (36 864
+  // warps that found nothing to do cost 37 us per iteration of the 4096-OCP batch).  ls_hdr[p] = entries of list
+  // p, ls_hdr[2 + p] = CTA ticket of cost pass p (its last CTA empties the list for the next iteration);
+  // list 0 = ls_list[0, 10 B), list 1 = ls_list[10 B, 20 B).
+  int* ls_hdr;
+  int* ls_list;
+  int fuse_accept;  // the cost pass that completes an OCP's line search also runs accept_body for it (aslr_solve)
 };
 
 // crocoddyl::raiseIfNaN
@@ -31,8 +40,11 @@ ASLR_HD void init_body(const SolverArgs& a, int b) {
   s.d1 = 0, s.d2 = 0, s.dg = 0, s.dq = 0, s.ffeas = 0;
   s.iter = 0, s.status = ASLR_OCP_RUNNING, s.is_feasible = a.opts.is_feasible ? 1 : 0, s.was_feasible = 0;
   s.recalc = 1, s.accepted = -1, s.src_slot = -1, s.n_backward_retries = 0;
-  s.full_steps = 0, s.n_logged = 0;
-  if (b == 0) a.buf.counters[0] = a.B;
+  s.full_steps = 0, s.n_logged = 0, s.ls_done = 0, s.reserved0 = 0;
+  if (b == 0) {
+    a.buf.counters[0] = a.B;
+    if (a.ls_hdr) a.ls_hdr[0] = 0, a.ls_hdr[1] = 0, a.ls_hdr[2] = 0, a.ls_hdr[3] = 0;
+  }
 }
 
 // contiguous rows of doubles moved in 16-byte pieces when the row length is even (the row start is then 16-byte
@@ -244,6 +256,9 @@ ASLR_HD void quasi_static_body(const DevProblem<N>& P, const double* x, const do
 // K3: one trial rollout = SolverDDP/FDDP/BoxDDP::forwardPass(alpha) (Appendix A.4) plus the
 // trial-dependent part of FDDP's expectedImprovement.  One thread per (OCP, alpha).
 // ---------------------------------------------------------------------------------------------
+#ifndef ASLR_ROLL_NBUF
+#define ASLR_ROLL_NBUF 2
+#endif
 #ifndef ASLR_ROLL_PIPE_MAX
 #define ASLR_ROLL_PIPE_MAX 16  // largest nu * nx whose rollout stages the next step's loads in shared memory
 #endif
@@ -255,8 +270,9 @@ struct RollStage {
   static constexpr bool ENABLED = (NU * NX <= ASLR_ROLL_PIPE_MAX) && (NU % 2 == 0) && (NX % 2 == 0);
   static constexpr int K = 0, XS = K + NU * NX, US = XS + NX, KF = US + NU, ROW = KF + NU + 2;
   static constexpr int THREADS = 32;
+  static constexpr int NBUF = ASLR_ROLL_NBUF;  // 2: copies run one step ahead of the recursion, 3: two steps
   static constexpr int BUF = ROW * THREADS;
-  static constexpr int CTA_DOUBLES = 2 * BUF;
+  static constexpr int CTA_DOUBLES = NBUF * BUF;
 #if defined(__CUDACC__)
   static __device__ __forceinline__ void cp16(double* dst, const double* src) {
     const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
@@ -272,11 +288,33 @@ struct RollStage {
     for (int i = 0; i < NU; i += 2) cp16(row + US + i, us + i), cp16(row + KF + i, kf + i);
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
-  static __device__ __forceinline__ void wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+  // wait until at most one (one_pending) or none of the most recent copy groups is still in flight
+  static __device__ __forceinline__ void wait(bool one_pending) {
+    if (one_pending)
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    else
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+  }
 #endif
 };
+// The trial (b, ai) has been rolled out: its cost may be wanted (alpha = 1: always; the others: only if the full
+// step turns out not to be taken -- the lazy line search of trial_cost_finish).
+ASLR_HD void ls_append(const SolverArgs& a, int b, int ai, int phase) {
+#if defined(__CUDA_ARCH__)
+  (void)phase;
+  if (a.ls_hdr) {
+    const int p = ai > 0 ? 1 : 0;
+    const int slot = atomicAdd(a.ls_hdr + p, 1);
+    a.ls_list[(size_t)p * ASLR_NUM_ALPHAS * a.B + slot] = b * ASLR_NUM_ALPHAS + ai;
+  }
+#else
+  (void)a, (void)b, (void)ai, (void)phase;
+#endif
+}
+
 template <int N, int NU, bool VSA>
-ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, int ai, double* stage = nullptr) {
+ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, int ai, double* stage = nullptr,
+                          int phase = 0) {
   constexpr int NX = 4 * N;
   const AslrOcpState& s = a.buf.state[b];
   if (s.status != ASLR_OCP_RUNNING) return;
@@ -311,7 +349,10 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
   // did not shorten them); holding them in registers instead spilled 200 bytes even at 254 registers.
 #if defined(__CUDA_ARCH__)
   const bool PIPE = RollStage<NX, NU>::ENABLED && stage != nullptr;
+  constexpr int AHEAD = RollStage<NX, NU>::NBUF - 1;  // how many steps the staged copies run ahead
   if (PIPE && T > 0) RollStage<NX, NU>::issue(stage, Kg, xs, us, kf);
+  if (PIPE && AHEAD > 1 && T > 1)
+    RollStage<NX, NU>::issue(stage + RollStage<NX, NU>::BUF, Kg + NU * NX, xs + NX, us + NU, kf + NU);
 #else
   const bool PIPE = false;
   (void)stage;
@@ -337,15 +378,16 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
     double dx[NX], fsv[NX], xsv[NX], wvv[NX], Kv[NU * NX], usv[NU], kfv[NU];
     if (PIPE) {
 #if defined(__CUDA_ARCH__)
-      double* row = stage + (t & 1) * RollStage<NX, NU>::BUF;
-      RollStage<NX, NU>::wait();
+      double* row = stage + (t % RollStage<NX, NU>::NBUF) * RollStage<NX, NU>::BUF;
+      RollStage<NX, NU>::wait(AHEAD > 1 && t + 1 < T);  // the group of step t + 1 may stay in flight
       ld_row<NU * NX>(Kv, row + RollStage<NX, NU>::K);
       ld_row<NX>(xsv, row + RollStage<NX, NU>::XS);
       ld_row<NU>(usv, row + RollStage<NX, NU>::US);
       ld_row<NU>(kfv, row + RollStage<NX, NU>::KF);
-      if (t + 1 < T)
-        RollStage<NX, NU>::issue(stage + ((t + 1) & 1) * RollStage<NX, NU>::BUF, Kg + (size_t)(t + 1) * NU * NX,
-                                 xs + (size_t)(t + 1) * NX, us + (size_t)(t + 1) * NU, kf + (size_t)(t + 1) * NU);
+      if (t + AHEAD < T)  // into the buffer that was read AHEAD - 1 steps ago (this step's own when AHEAD = 1)
+        RollStage<NX, NU>::issue(stage + ((t + AHEAD) % RollStage<NX, NU>::NBUF) * RollStage<NX, NU>::BUF,
+                                 Kg + (size_t)(t + AHEAD) * NU * NX, xs + (size_t)(t + AHEAD) * NX,
+                                 us + (size_t)(t + AHEAD) * NU, kf + (size_t)(t + AHEAD) * NU);
 #endif
     } else {
       ld_row<NX>(xsv, xs + (size_t)t * NX);
@@ -403,6 +445,7 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
   tr[1] = dv;
   tr[2] = ok ? 1.0 : 0.0;
   tr[3] = 0.0;
+  ls_append(a, b, ai, phase);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -507,6 +550,18 @@ ASLR_HD void trial_cost_body(const DevProblem<N>& P, const SolverArgs& a, int b,
 // K4: line-search decision + regularisation + stopping test for one OCP (the tail of
 // SolverDDP::solve / SolverFDDP::solve, Appendix A.1).  One thread per OCP.
 // ---------------------------------------------------------------------------------------------
+// A trial record as it is in L2: when the decision rides on the trial-cost kernel, the records of an OCP's other
+// step lengths were written by other warps of the same launch, and this SM's L1 may hold an older copy of their
+// cache lines (four 32-byte records share one) -- L1 is not coherent across SMs within a kernel.
+ASLR_HD void ld_trial(const double* tr, double* out) {
+#if defined(__CUDA_ARCH__)
+  const double2 lo = __ldcg(reinterpret_cast<const double2*>(tr)), hi = __ldcg(reinterpret_cast<const double2*>(tr) + 1);
+  out[0] = lo.x, out[1] = lo.y, out[2] = hi.x, out[3] = hi.y;
+#else
+  out[0] = tr[0], out[1] = tr[1], out[2] = tr[2], out[3] = tr[3];
+#endif
+}
+
 ASLR_HD void accept_body(const SolverArgs& a, int b, int* n_done) {
   AslrOcpState& s = a.buf.state[b];
   if (s.status != ASLR_OCP_RUNNING) {
@@ -520,7 +575,8 @@ ASLR_HD void accept_body(const SolverArgs& a, int b, int* n_done) {
   for (int ai = 0; ai < ASLR_NUM_ALPHAS; ++ai) {
     const double alpha = 1.0 / (double)(1 << ai);
     steplength = alpha;
-    const double* tr = a.buf.trial + ((size_t)b * ASLR_NUM_ALPHAS + ai) * 4;
+    double tr[4];
+    ld_trial(a.buf.trial + ((size_t)b * ASLR_NUM_ALPHAS + ai) * 4, tr);
     if (tr[2] == 0.0) continue;  // the rollout threw (NaN / inf): try the next step length
     s.cost_try = tr[0];
     const TrialTest tt = trial_accept_test(s, o, ai, tr);

@@ -35,6 +35,7 @@ extern "C" {
 #define ASLR_MAX_NU (2 * ASLR_MAX_DOF)
 #define ASLR_MAX_COST_TERMS 6
 #define ASLR_NUM_ALPHAS 10 /* crocoddyl: alphas = 2^-k, k = 0..9 */
+#define ASLR_COUNTER_INTS 40 /* fixed part of AslrSolverBuffers.counters */
 
 typedef enum AslrStatus {
   ASLR_OK = 0,
@@ -189,6 +190,8 @@ typedef struct AslrOcpState {
                           lengths the forward pass rolls out speculatively, never the result */
   int32_t n_logged;    /* rows of `log` written for this OCP = iterations whose callbacks crocoddyl would have run
                           (an iteration that ends with regularisation at reg_max returns before the callbacks) */
+  int32_t ls_done;     /* line search: trial costs of this OCP finished in the current pass (device scheduling only) */
+  int32_t reserved0;
 } AslrOcpState;
 
 typedef enum AslrOcpStatus {
@@ -221,7 +224,9 @@ typedef struct AslrSolverBuffers {
   double* trial;   /* [B][ASLR_NUM_ALPHAS][4]: cost_try, dv, ok(1/0), alpha = 1 record only: step taken (1/0) */
   double* log;     /* [B][maxiter][ASLR_LOG_FIELDS], optional */
   AslrOcpState* state; /* [B] */
-  int32_t* counters;   /* [4]: counters[0] = OCPs still running */
+  int32_t* counters;   /* [ASLR_COUNTER_INTS + 2 * ASLR_NUM_ALPHAS * B] solver scratch: counters[k], k < 8 = OCPs still
+                          running in sub-batch k (counters[0] = the whole batch unless aslr_solve cut it); then the
+                          work-list counts and the work lists of the line search (trials whose cost is wanted) */
 } AslrSolverBuffers;
 
 typedef struct AslrSolveResult {

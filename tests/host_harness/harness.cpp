@@ -58,6 +58,7 @@ static int solve_t(const AslrProblemDesc* desc, const AslrBatch* batch, const As
   a.x0 = batch->x0, a.K_ocp = batch->K_ocp, a.mref_ocp = batch->mref_ocp;
   a.buf = *buf;
   a.opts = *opts;
+  a.ls_hdr = nullptr, a.ls_list = nullptr, a.fuse_accept = 0;  // the work lists belong to the CUDA kernels
   std::vector<double> sm(BwdSmem<NX, NU>::SIZE), rs(RollSmem<N, NU>::SIZE), mc(ModelConst<N>::SIZE);
   for (int b = 0; b < a.B; ++b) init_body(a, b);
   int it = 0;
