@@ -13,6 +13,7 @@ MAX_COST_TERMS = 6
 NUM_ALPHAS = 10
 LOG_FIELDS = 8
 COUNTER_INTS = 40
+STATIC_SCRATCH_BYTES = 64 << 20
 
 (COST_NONE, COST_FRAME_PLACEMENT, COST_STATE, COST_CONTROL, COST_STIFFNESS, COST_DOUBLE_PENDULUM,
  COST_RESIDUAL_DOUBLE_PENDULUM) = range(7)
@@ -137,6 +138,7 @@ _PROTOS = {
     "aslr_solve": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(SolverOpts), C.POINTER(SolverBuffers),
                              C.POINTER(SolveResult), C.c_void_p]),
     "aslr_solve_host": (C.c_int, [C.c_void_p, C.POINTER(HostSolveIO), C.POINTER(SolverOpts), C.POINTER(SolveResult)]),
+    "aslr_solve_static": (C.c_int, [C.c_void_p, C.POINTER(Batch), C.POINTER(SolverOpts)] + [C.c_void_p] * 6),
 }
 
 EXPORTED_SYMBOLS = tuple(sorted(_PROTOS))

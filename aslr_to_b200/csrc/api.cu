@@ -671,4 +671,98 @@ int aslr_solve_host(AslrProblem* p, const AslrHostSolveIO* io, const AslrSolverO
   return ASLR_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// aslr_solve_static: solver.solve(xs, us, maxiter) that ALLOCATES NOTHING (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight
+// serving loops, harnesses that forbid it).  Every solver array other than the caller's inputs / outputs lives in
+// one file-scope device array of ASLR_STATIC_SCRATCH_BYTES; every GPU that loads the library holds it until exit.
+// In host code the array's NAME is a host-side stand-in, not a device address: its address is taken once per
+// device with cudaGetSymbolAddress (that device current) and only that pointer is handed to the kernels.
+// All calls share the array and it keeps the last call's contents: what must start at zero is cleared on the
+// caller's stream at the top of the call, and two calls that overlap on the GPU (different streams, or two host
+// threads) RACE on it -- the caller serialises them.  No host synchronisation, no streams / events / pinned memory of
+// the handle: exactly opts->maxiter iterations are enqueued on `stream` (an OCP that has finished rides along as a
+// no-op), so the call is asynchronous and its launch sequence does not depend on the data.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[ASLR_STATIC_SCRATCH_BYTES];
+
+namespace {
+std::mutex g_static_mu;
+double* g_static_ptr[64] = {nullptr};  // device address of g_static_scratch, per device ordinal
+
+// the device address of the scratch array on the CURRENT device (looked up once per device)
+int static_scratch_address(int device, double** out) {
+  if (device < 0 || device >= 64) return fail(ASLR_ERR_UNSUPPORTED, "device ordinal beyond 63%s");
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_ptr[device]) {
+    void* q = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&q, g_static_scratch);
+    if (e != cudaSuccess) return cuda_fail(e);
+    g_static_ptr[device] = static_cast<double*>(q);
+  }
+  *out = g_static_ptr[device];
+  return ASLR_OK;
+}
+}  // namespace
+
+int aslr_solve_static(const AslrProblem* pc, const AslrBatch* batch, const AslrSolverOpts* opts, double* xs, double* us,
+                      AslrOcpState* state, double* Kgain, double* kff, void* stream) {
+  AslrProblem* p = const_cast<AslrProblem*>(pc);
+  if (!p || !batch || !opts || !xs || !us || !state) return fail(ASLR_ERR_INVALID, "null argument%s");
+  if (batch->B <= 0 || batch->T <= 0) return fail(ASLR_ERR_INVALID, "B and T must be positive%s");
+  if (!batch->x0) return fail(ASLR_ERR_INVALID, "x0 is required%s");
+  if (opts->kind < ASLR_SOLVER_DDP || opts->kind > ASLR_SOLVER_BOXDDP) return fail(ASLR_ERR_INVALID, "unknown solver kind%s");
+  if (opts->maxiter < 0) return fail(ASLR_ERR_INVALID, "negative maxiter%s");
+  DeviceGuard dg(p->device);
+  if (!dg.ok) return fail(ASLR_ERR_CUDA, "cannot make the handle's device current%s");
+  // ---- carve the static array: segment sizes in doubles, each rounded up to 32 doubles (256 bytes)
+  const size_t B = batch->B, T = batch->T, nx = p->nx, nu = p->nu, rec = aslr_record_doubles(p->nx, p->nu);
+  enum { XNEXT, KCOST, DERIV, FS, KG, KF, VX, VXXFS, QU, QUUK, XTRY, UTRY, TRIAL, CNT, NSEG };
+  size_t sz[NSEG];
+  sz[XNEXT] = B * T * nx, sz[KCOST] = B * (T + 1), sz[DERIV] = B * (T + 1) * rec, sz[FS] = B * (T + 1) * nx;
+  sz[KG] = Kgain ? 0 : B * T * nu * nx, sz[KF] = kff ? 0 : B * T * nu;
+  sz[VX] = B * (T + 1) * nx, sz[VXXFS] = B * (T + 1) * nx, sz[QU] = B * T * nu, sz[QUUK] = B * T * nu;
+  sz[XTRY] = B * ASLR_NUM_ALPHAS * (T + 1) * nx, sz[UTRY] = B * ASLR_NUM_ALPHAS * T * nu;
+  sz[TRIAL] = B * ASLR_NUM_ALPHAS * 4, sz[CNT] = (ASLR_COUNTER_INTS + 2 * ASLR_NUM_ALPHAS * B + 1) / 2;
+  size_t off[NSEG], total = 0;
+  for (int k = 0; k < NSEG; ++k) off[k] = total, total += (sz[k] + 31) & ~(size_t)31;
+  if (total * sizeof(double) > (size_t)ASLR_STATIC_SCRATCH_BYTES) {
+    std::snprintf(g_err, sizeof(g_err),
+                  "aslr_solve_static: this batch needs %zu bytes of solver scratch, the static array holds %zu "
+                  "(ASLR_STATIC_SCRATCH_BYTES); use aslr_solve with caller-allocated buffers",
+                  total * sizeof(double), (size_t)ASLR_STATIC_SCRATCH_BYTES);
+    return ASLR_ERR_UNSUPPORTED;
+  }
+  double* D = nullptr;
+  if (int rc = static_scratch_address(p->device, &D)) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  AslrSolverBuffers buf;
+  std::memset(&buf, 0, sizeof(buf));
+  buf.xs = xs, buf.us = us, buf.state = state;
+  buf.xnext = D + off[XNEXT], buf.knot_cost = D + off[KCOST], buf.deriv = D + off[DERIV], buf.fs = D + off[FS];
+  buf.Kgain = Kgain ? Kgain : D + off[KG], buf.kff = kff ? kff : D + off[KF];
+  buf.Vx = D + off[VX], buf.Vxxfs = D + off[VXXFS], buf.Qu = D + off[QU], buf.Quuk = D + off[QUUK];
+  buf.xs_try = D + off[XTRY], buf.us_try = D + off[UTRY], buf.trial = D + off[TRIAL];
+  buf.counters = reinterpret_cast<int32_t*>(D + off[CNT]);
+  SolverArgs a;
+  if (int rc = make_args(p, batch, opts, &buf, 0, &a)) return rc;
+  // the array keeps the last call's contents: the running words, the work-list counts and the trial records (whose
+  // "full step taken" flags steer the second rollout phase) start at zero
+  cudaError_t e = cudaMemsetAsync(buf.counters, 0, sz[CNT] * sizeof(double), s);
+  if (e == cudaSuccess) e = cudaMemsetAsync(buf.trial, 0, sz[TRIAL] * sizeof(double), s);
+  if (e != cudaSuccess) return cuda_fail(e);
+  if (launch_init(a, s)) return cuda_fail(cudaGetLastError());
+  a.fuse_accept = 1;
+  for (int it = 0; it < opts->maxiter; ++it) {
+    a.iter = it;
+    if (p->fn.calcdiff(p->dev, a, s) || p->fn.backward(p->dev, a, s) || p->fn.rollout(p->dev, a, s))
+      return cuda_fail(cudaGetLastError());
+  }
+  if (opts->maxiter > 0) {  // adopt the candidates accepted in the last iteration (setCandidate)
+    a.iter = opts->maxiter;
+    if (p->fn.calcdiff(p->dev, a, s) || launch_accept(a, s)) return cuda_fail(cudaGetLastError());
+  }
+  return ASLR_OK;
+}
+
 }  // extern "C"

@@ -312,6 +312,23 @@ typedef struct AslrHostSolveIO {
 } AslrHostSolveIO;
 int aslr_solve_host(AslrProblem* p, const AslrHostSolveIO* io, const AslrSolverOpts* opts, AslrSolveResult* result);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * aslr_solve for all B OCPs with NO allocation of any kind: the caller passes the inputs / outputs as device
+ * pointers -- batch (x0, K_ocp, mref_ocp), xs [B][T+1][nx] and us [B][T][nu] (in: warm start, out: solution), state [B],
+ * optionally Kgain [B][T][nu][nx] and kff [B][T][nu] (NULL = kept internal) -- and every other solver array lives in one
+ * file-scope device array of ASLR_STATIC_SCRATCH_BYTES that every GPU that loads the library holds until exit.
+ * A batch that needs more returns ASLR_ERR_UNSUPPORTED with the sizes in aslr_last_error() (2-DOF SEA, T = 100:
+ * about 0.17 MB per OCP, i.e. up to ~390 OCPs; 7-DOF SEA, T = 200: about 4.3 MB per OCP).
+ * Asynchronous on `stream` and data-independent: exactly opts->maxiter iterations are enqueued, no host
+ * synchronisation, no streams / events / pinned memory of the handle (opts->poll_every is ignored); read `state`
+ * after synchronising the stream.  Results are bit-identical to aslr_solve.
+ * All calls share the array, which keeps the last call's contents (what must start at zero is cleared on `stream`
+ * by the call): calls that overlap on the GPU -- other streams, other host threads, other handles -- RACE. */
+#define ASLR_STATIC_SCRATCH_BYTES (64u << 20)
+int aslr_solve_static(const AslrProblem* p, const AslrBatch* batch, const AslrSolverOpts* opts, double* xs, double* us,
+                      AslrOcpState* state, double* Kgain, double* kff, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
