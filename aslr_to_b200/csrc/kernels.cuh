@@ -211,6 +211,8 @@ template <int N, int NU, bool VSA>
 __global__ void __launch_bounds__((N <= 2) ? ASLR_ROLL_THREADS : 64, (N <= 2) ? ASLR_ROLL_MINB : 1) rollout_kernel(const __grid_constant__ DevProblem<N> P, const SolverArgs a, const int phase) {
   // threads [0, B) are the alpha = 1 trials (packed: in the steady state they are the only ones that run, see
   // rollout_narrow), threads [B, 10 B) the other nine step lengths of each OCP; phase 1 launches only the latter
+  // first kernel of a forward pass: list 1 of the line search is appended to by the cost passes only (solver_dev.cuh)
+  if (phase == 0 && blockIdx.x == 0 && threadIdx.x == 0 && a.ls_hdr) a.ls_hdr[1] = 0;
   const long g = (long)blockIdx.x * blockDim.x + threadIdx.x + (phase == 0 ? 0 : a.B);
   if (g >= (long)a.B * ASLR_NUM_ALPHAS) return;
   const int b = (g < a.B) ? (int)g : (int)((g - a.B) / (ASLR_NUM_ALPHAS - 1));
@@ -232,6 +234,7 @@ __global__ void __launch_bounds__(GS * TRIALS, ASLR_ROLLC_MINB) rollout_coop_ker
   extern __shared__ double smem[];
   for (int i = threadIdx.x; i < N; i += blockDim.x) model_const_fill<N>(P, smem, i);
   __syncthreads();
+  if (phase <= 0 && blockIdx.x == 0 && threadIdx.x == 0 && a.ls_hdr) a.ls_hdr[1] = 0;  // as rollout_kernel
   const int w = threadIdx.x / GS;
   // trials [0, B) are alpha = 1 of every OCP, [B, 10 B) the other step lengths (see rollout_kernel / rollout_wanted)
   const long trial = (long)blockIdx.x * TRIALS + w + (phase <= 0 ? 0 : a.B);
@@ -246,6 +249,30 @@ __global__ void __launch_bounds__(GS * TRIALS, ASLR_ROLLC_MINB) rollout_coop_ker
                                             b, ai);
 }
 
+#ifndef ASLR_COST_CTA_MAXT
+#define ASLR_COST_CTA_MAXT 512  // longest horizon (T + 1 knots) the CTA-per-trial mode of the cost kernel handles
+#endif
+// What follows the cost of trial (b, ai) in cost pass `pass` (one thread): see linesearch_cost_kernel.
+__device__ __forceinline__ void linesearch_after_cost(const SolverArgs& a, int b, int pass, const double* tr) {
+  if (pass == 0) {
+    if (tr[3] != 0.0) {  // full step taken (written by this thread just now): the line search is over
+      if (a.fuse_accept) accept_body(a, b, a.buf.counters);
+    } else {             // the other nine step lengths are (or will be, rollout phase 1) rolled out: cost them
+      const int slot = atomicAdd(a.ls_hdr + 1, ASLR_NUM_ALPHAS - 1);
+      int* l1 = a.ls_list + (size_t)ASLR_NUM_ALPHAS * a.B + slot;
+      for (int k = 1; k < ASLR_NUM_ALPHAS; ++k) l1[k - 1] = b * ASLR_NUM_ALPHAS + k;
+    }
+  } else if (a.fuse_accept) {
+    AslrOcpState& s = a.buf.state[b];
+    __threadfence();  // this trial's record before the count
+    if (atomicAdd(&s.ls_done, 1) + 1 == ASLR_NUM_ALPHAS - 1) {
+      __threadfence();  // the other trials' records after the count
+      s.ls_done = 0;
+      accept_body(a, b, a.buf.counters);
+    }
+  }
+}
+
 // K3b: costs of the trial trajectories + (in aslr_solve) the line-search decision.  Persistent warps walk the work
 // list of the pass (solver_dev.cuh: ls_append): one warp per trial, lanes take the knots 32 at a time, the costs are
 // then added in knot order (shuffle broadcast, every lane keeps the same running total) so the sum equals the
@@ -253,7 +280,7 @@ __global__ void __launch_bounds__(GS * TRIALS, ASLR_ROLLC_MINB) rollout_coop_ker
 // nine step lengths, only for the OCPs whose full step was not taken (lazy line search: the speculative rollouts of
 // an OCP that took alpha = 1 are never costed).  The warp that completes an OCP's line search -- alpha = 1 taken in
 // pass 0, or the ninth trial of pass 1 -- runs accept_body for it (fuse_accept): the decision needs the costs of
-// that OCP and nothing else, so it does not need a kernel of its own.  The last CTA to finish empties the list.
+// that OCP and nothing else, so it does not need a kernel of its own.
 template <int N, int NU, bool VSA>
 __global__ void __launch_bounds__(128) linesearch_cost_kernel(const __grid_constant__ DevProblem<N> P, const SolverArgs a,
                                                               const int pass) {
@@ -262,12 +289,35 @@ __global__ void __launch_bounds__(128) linesearch_cost_kernel(const __grid_const
   const int nwarps = (int)((gridDim.x * blockDim.x) >> 5);
   const int count = a.ls_hdr[pass];
   const int* list = a.ls_list + (size_t)pass * ASLR_NUM_ALPHAS * a.B;
+  // Short list (the straggler regime: fewer trials than CTAs): one CTA per trial, its four warps take a quarter of
+  // the knots each and thread 0 adds the knot costs in knot order -- the same floating-point sum in a quarter of
+  // the rounds (at T = 100: one round of the knot-cost chain instead of four).
+  if (count <= (int)gridDim.x && a.T + 1 <= ASLR_COST_CTA_MAXT) {
+    __shared__ double kc[ASLR_COST_CTA_MAXT];
+    if ((int)blockIdx.x < count) {
+      const int id = list[blockIdx.x];
+      const int b = id / ASLR_NUM_ALPHAS, ai = id % ASLR_NUM_ALPHAS;
+      double* tr = a.buf.trial + ((size_t)b * ASLR_NUM_ALPHAS + ai) * 4;
+      const bool ran = tr[2] != 0.0;
+      if (ran)
+        for (int t = threadIdx.x; t <= a.T; t += blockDim.x) kc[t] = trial_knot_cost<N, NU, VSA>(P, a, b, ai, t);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        if (ran) {
+          double total = 0.0;
+          for (int t = 0; t <= a.T; ++t) total += kc[t];
+          trial_cost_finish(a, b, ai, total);
+        }
+        linesearch_after_cost(a, b, pass, tr);
+      }
+    }
+    if (pass == 1 && blockIdx.x == 0 && threadIdx.x == 0) a.ls_hdr[0] = 0;
+    return;
+  }
   for (int i = warp; i < count; i += nwarps) {
     const int id = list[i];
     const int b = id / ASLR_NUM_ALPHAS, ai = id % ASLR_NUM_ALPHAS;
     double* tr = a.buf.trial + ((size_t)b * ASLR_NUM_ALPHAS + ai) * 4;
-    const double* tr0 = a.buf.trial + (size_t)b * ASLR_NUM_ALPHAS * 4;  // the alpha = 1 record (final since pass 0)
-    if (pass == 1 && tr0[3] != 0.0) continue;  // the full step was taken: this trial was speculation
     if (tr[2] != 0.0) {  // the rollout did not throw
       double total = 0.0;
       for (int base = 0; base <= a.T; base += 32) {
@@ -278,26 +328,10 @@ __global__ void __launch_bounds__(128) linesearch_cost_kernel(const __grid_const
       }
       if (lane == 0) trial_cost_finish(a, b, ai, total);
     }
-    if (lane == 0 && a.fuse_accept) {
-      AslrOcpState& s = a.buf.state[b];
-      if (pass == 0) {
-        if (tr[3] != 0.0) accept_body(a, b, a.buf.counters);  // full step taken (written by this thread just now)
-      } else {
-        __threadfence();  // this trial's record before the count
-        if (atomicAdd(&s.ls_done, 1) + 1 == ASLR_NUM_ALPHAS - 1) {
-          __threadfence();  // the other trials' records after the count
-          s.ls_done = 0;
-          accept_body(a, b, a.buf.counters);
-        }
-      }
-    }
+    if (lane == 0) linesearch_after_cost(a, b, pass, tr);
   }
-  // every CTA has read `count` by the time it gets here: the last one to arrive empties the list
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    if (atomicAdd(a.ls_hdr + 2 + pass, 1) == (int)gridDim.x - 1) a.ls_hdr[pass] = 0, a.ls_hdr[2 + pass] = 0;
-  }
+  // list 0 is not read or appended to during pass 1: empty it for the next forward pass
+  if (pass == 1 && blockIdx.x == 0 && threadIdx.x == 0) a.ls_hdr[0] = 0;
 }
 
 // quasiStatic of every running knot: one thread per (OCP, knot)
@@ -439,17 +473,21 @@ struct Launch {
         <<<(unsigned)((total + threads - 1) / threads), threads, stage_bytes(threads, COMPACT), s>>>(P, a);
     return launch_status();
   }
-  // grid of the persistent trial-cost kernel: enough warps for every trial of a small batch, at most three CTAs
-  // per SM (166 registers per thread) otherwise
-  static unsigned cost_blocks(long trials) {
+  // grid of the trial-cost kernel.  Pass 0 (alpha = 1 of every running OCP: the list is full whenever the batch
+  // is) gets a warp per possible trial; pass 1 (usually empty or short: only OCPs whose full step failed) at most
+  // three CTAs per SM, whose warps walk the list
+  static unsigned cost_blocks(long trials, bool cap) {
     static int sms = 0;
     if (sms == 0) {
       int dev = 0;
       cudaGetDevice(&dev);
       if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
     }
-    const long want = (trials + 3) / 4, cap = 3L * sms;
-    return (unsigned)(want < 1 ? 1 : (want < cap ? want : cap));
+    // a warp per trial; small batches get a CTA per trial (the kernel's short-list mode: count <= CTAs)
+    long want = (trials + 3) / 4;
+    const long small = trials < 64 ? trials : 64, lim = 3L * sms;
+    if (want < small) want = small;
+    return (unsigned)(want < 1 ? 1 : ((cap && want > lim) ? lim : want));
   }
   static int rollout(const void* Pv, const SolverArgs& a, cudaStream_t s) {
     const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
@@ -461,18 +499,18 @@ struct Launch {
       if (allow_smem(k, bytes)) return -2;
       k<<<(unsigned)((total + TRIALS - 1) / TRIALS), GS * TRIALS, bytes, s>>>(P, a, -1);
       if (launch_status()) return -2;
-      linesearch_cost_kernel<N, NU, VSA><<<cost_blocks(a.B), 128, 0, s>>>(P, a, 0);
-      linesearch_cost_kernel<N, NU, VSA><<<cost_blocks(total - a.B), 128, 0, s>>>(P, a, 1);
+      linesearch_cost_kernel<N, NU, VSA><<<cost_blocks(a.B, false), 128, 0, s>>>(P, a, 0);
+      linesearch_cost_kernel<N, NU, VSA><<<cost_blocks(total - a.B, true), 128, 0, s>>>(P, a, 1);
       return launch_status();
     } else {
       // two-phase speculative line search (solver_dev.cuh: rollout_wanted)
       const int threads = ASLR_ROLL_THREADS;
       rollout_kernel<N, NU, VSA><<<(unsigned)((total + threads - 1) / threads), threads, 0, s>>>(P, a, 0);
       if (launch_status()) return -2;
-      linesearch_cost_kernel<N, NU, VSA><<<cost_blocks(a.B), 128, 0, s>>>(P, a, 0);
+      linesearch_cost_kernel<N, NU, VSA><<<cost_blocks(a.B, false), 128, 0, s>>>(P, a, 0);
       rollout_kernel<N, NU, VSA><<<(unsigned)((total - a.B + threads - 1) / threads), threads, 0, s>>>(P, a, 1);
       if (launch_status()) return -2;
-      linesearch_cost_kernel<N, NU, VSA><<<cost_blocks(total - a.B), 128, 0, s>>>(P, a, 1);
+      linesearch_cost_kernel<N, NU, VSA><<<cost_blocks(total - a.B, true), 128, 0, s>>>(P, a, 1);
       return launch_status();
     }
   }

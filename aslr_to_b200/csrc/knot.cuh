@@ -183,7 +183,7 @@ struct KnotDeriv {
 };
 
 #ifndef ASLR_TWO_LINK_COFACTOR
-#define ASLR_TWO_LINK_COFACTOR 0  // 1: 2 x 2 inverse by cofactors instead of Cholesky (tuning experiment)
+#define ASLR_TWO_LINK_COFACTOR 1  // 2 x 2 inverse of M by cofactors (0: Cholesky, as the larger models)
 #endif
 #ifndef ASLR_TWO_LINK
 #define ASLR_TWO_LINK 1  // N = 2: closed-form rigid-body terms (TwoLinkConst, problem_dev.cuh) instead of the recursion
@@ -249,7 +249,7 @@ ASLR_HD void knot_core(const DevProblem<N>& P, const DevCostSum<N>& C, const dou
   SI Y[N];
   double sq[N], cq[N];
 #pragma unroll
-  for (int i = 0; i < N; ++i) sincos(ql[i], &sq[i], &cq[i]);
+  for (int i = 0; i < N; ++i) joint_sincos(ql[i], &sq[i], &cq[i]);
   if (!TWO || COSTS) {
 #pragma unroll
     for (int i = 0; i < N; ++i) {
@@ -680,7 +680,7 @@ ASLR_HD double knot_cost_only(const DevProblem<N>& P, const DevCostSum<N>& C, co
 #pragma unroll
   for (int i = 0; i < N; ++i) {
     double s, c;
-    sincos(x[i], &s, &c);
+    joint_sincos(x[i], &s, &c);
     const double omc = 1.0 - c;
     M3 Rl;
 #pragma unroll

@@ -146,7 +146,7 @@ ASLR_HD void rollout_coop_body(const Grp& g, double* sm, const double* jc, const
       xt[(size_t)t * NX + i] = xi;
       if (i < N) {  // same lane, same value: q_l[i]
         double sn, cs;
-        sincos(xi, &sn, &cs);
+        joint_sincos(xi, &sn, &cs);
         const double omc = 1.0 - cs;
         const double* c = jc + i * JC::SIZE;
 #pragma unroll

@@ -5,6 +5,8 @@
 // examples/two_dof_vsa_boxddp.py:69-81 and examples/double_pendulum.py:55,70.
 #pragma once
 
+#include <string.h>
+
 #include "knot.cuh"
 
 namespace aslr {
@@ -16,12 +18,13 @@ struct SolverArgs {
   const double* mref_ocp;
   AslrSolverBuffers buf;
   AslrSolverOpts opts;
-  // Line-search work lists (CUDA kernels only; null in the host emulation).  Every trial that is actually rolled
-  // out appends its id (b * ASLR_NUM_ALPHAS + ai) to list 0 (alpha = 1) or list 1 (the other step lengths), so the
-  // trial-cost passes walk exactly the trials that exist instead of launching a warp per possible trial (36 864
-  // warps that found nothing to do cost 37 us per iteration of the 4096-OCP batch).  ls_hdr[p] = entries of list
-  // p, ls_hdr[2 + p] = CTA ticket of cost pass p (its last CTA empties the list for the next iteration);
-  // list 0 = ls_list[0, 10 B), list 1 = ls_list[10 B, 20 B).
+  // Line-search work lists (CUDA kernels only; null in the host emulation), so that the trial-cost passes walk
+  // exactly the trials whose cost is wanted instead of launching a warp per possible trial (36 864 warps that found
+  // nothing to do cost 37 us per iteration of the 4096-OCP batch).  List 0 = ls_list[0, 10 B): the alpha = 1 trial
+  // of every running OCP, appended by its rollout; list 1 = ls_list[10 B, 20 B): the other nine step lengths of the
+  // OCPs whose full step was not taken, appended by cost pass 0.  ls_hdr[p] = entries of list p.  Who empties them:
+  // list 1 is only appended to by cost pass 0 (and later), so the first rollout kernel of a forward pass clears it;
+  // list 0 is only appended to by that rollout kernel, so cost pass 1 clears it.
   int* ls_hdr;
   int* ls_list;
   int fuse_accept;  // the cost pass that completes an OCP's line search also runs accept_body for it (aslr_solve)
@@ -29,6 +32,17 @@ struct SolverArgs {
 
 // crocoddyl::raiseIfNaN
 ASLR_HD bool bad_value(double v) { return isnan(v) || isinf(v) || v >= 1e30; }
+// max(m, high word of |v|): the screen in front of bad_value
+ASLR_HD unsigned umax_hi(unsigned m, double v) {
+#if defined(__CUDA_ARCH__)
+  const unsigned h = (unsigned)__double2hiint(v) & 0x7fffffffu;
+#else
+  unsigned long long bits;
+  memcpy(&bits, &v, sizeof(bits));
+  const unsigned h = (unsigned)(bits >> 32) & 0x7fffffffu;
+#endif
+  return h > m ? h : m;
+}
 
 // ---------------------------------------------------------------------------------------------
 // solve(): initial state of one OCP (SolverDDP::solve prologue, Appendix A.1)
@@ -297,15 +311,14 @@ struct RollStage {
   }
 #endif
 };
-// The trial (b, ai) has been rolled out: its cost may be wanted (alpha = 1: always; the others: only if the full
-// step turns out not to be taken -- the lazy line search of trial_cost_finish).
+// The trial (b, ai) has been rolled out.  The cost of alpha = 1 is always wanted: list 0.  The others are costed
+// only if the full step turns out not to be taken (lazy line search): cost pass 0 lists them then.
 ASLR_HD void ls_append(const SolverArgs& a, int b, int ai, int phase) {
 #if defined(__CUDA_ARCH__)
   (void)phase;
-  if (a.ls_hdr) {
-    const int p = ai > 0 ? 1 : 0;
-    const int slot = atomicAdd(a.ls_hdr + p, 1);
-    a.ls_list[(size_t)p * ASLR_NUM_ALPHAS * a.B + slot] = b * ASLR_NUM_ALPHAS + ai;
+  if (a.ls_hdr && ai == 0) {
+    const int slot = atomicAdd(a.ls_hdr, 1);
+    a.ls_list[slot] = b * ASLR_NUM_ALPHAS;
   }
 #else
   (void)a, (void)b, (void)ai, (void)phase;
@@ -340,6 +353,14 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
   double x[NX], xn[NX], u[NU];
 #pragma unroll
   for (int i = 0; i < NX; ++i) x[i] = a.x0[(size_t)b * NX + i];
+  // the OCP's stiffness matrix is read once, not at every knot (a global load on the chain: 15 % of the stall
+  // samples of the full-batch rollout were its first use)
+  double Kreg[N * N];
+  if (Kocp) {
+#pragma unroll
+    for (int i = 0; i < N * N; ++i) Kreg[i] = Kocp[i];
+    Kocp = Kreg;
+  }
   double cost_try = 0.0, dv = 0.0;
   bool ok = true;
   // Staged loads (CUDA kernel, small models): the gains, candidate state and controls of step t + 1 are copied
@@ -420,17 +441,23 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
     double c;
     KnotDeriv<N, NU> unused;
     knot_core<N, NU, VSA, false, false>(P, P.run, P.dt, x, u, Kocp, mref, xn, c, unused, nullptr, nullptr, nullptr);
-    double xmax = 0.0;
-    bool xnan = false;
+    // crocoddyl's raiseIfNaN(|xnext|_inf): NaN, inf or >= 1e30.  The high word of |v| as an integer orders like |v|
+    // (NaN and inf have the largest exponents), so one integer max and one compare decide
+    unsigned mhi = 0u;
 #pragma unroll
     for (int i = 0; i < NX; ++i) {
-      xmax = fmax(xmax, fabs(xn[i]));
-      xnan = xnan || isnan(xn[i]);
+      mhi = umax_hi(mhi, xn[i]);
       x[i] = xn[i];
     }
-    if (xnan || bad_value(xmax)) {
-      ok = false;
-      break;
+    if (mhi >= 0x46293E59u) {  // 1e30 = 0x46293E59 39A08CEA: possible, run the exact test
+      double xmax = 0.0;
+      bool xnan = false;
+#pragma unroll
+      for (int i = 0; i < NX; ++i) xmax = fmax(xmax, fabs(xn[i])), xnan = xnan || isnan(xn[i]);
+      if (xnan || bad_value(xmax)) {
+        ok = false;
+        break;
+      }
     }
   }
   if (ok) {

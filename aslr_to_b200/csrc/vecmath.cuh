@@ -35,6 +35,42 @@ ASLR_HD double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 ASLR_HD V3 cross(V3 a, V3 b) { return V3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
 ASLR_HD V3 ld3(const double* p) { return V3{p[0], p[1], p[2]}; }
 
+// sin and cos of a joint angle.  The library sincos is 76 instructions on the sequential chain of the rollout (two
+// per knot: 27 % of its instructions at n = 2); joint angles are small numbers, so the common case is done here:
+// Cody-Waite reduction by pi / 2 (exact product under the FMA, two-term constant) and the fdlibm kernel polynomials
+// on [-pi/4, pi/4] (< 1 ulp), both functions evaluated and routed by quadrant without a branch.  Beyond |x| = 1e4 (a
+// diverging trial rollout) the library routine takes over, so every input keeps a correctly reduced argument.
+// One function for every kernel and for the host build: the trial rollout, the cost pass and the derivative sweep
+// see bit-identical link poses.
+ASLR_HD void joint_sincos(double x, double* s, double* c) {
+  if (!(fabs(x) < 1.0e4)) {  // also NaN / inf
+    sincos(x, s, c);
+    return;
+  }
+  const double kf = rint(x * 0.63661977236758134308);  // 2 / pi
+  double r = fma(-kf, 1.57079632679489655800e+00, x);   // pi / 2, high part
+  r = fma(-kf, 6.12323399573676603587e-17, r);          // pi / 2, low part
+  const int q = (int)kf;
+  const double z = r * r;
+  double ps = 1.58969099521155010221e-10;
+  ps = fma(ps, z, -2.50507602534068634195e-08);
+  ps = fma(ps, z, 2.75573137070700676789e-06);
+  ps = fma(ps, z, -1.98412698298579493134e-04);
+  ps = fma(ps, z, 8.33333333332248946124e-03);
+  ps = fma(ps, z, -1.66666666666666324348e-01);
+  const double sr = fma(r * z, ps, r);
+  double pc = -1.13596475577881948265e-11;
+  pc = fma(pc, z, 2.08757232129817482790e-09);
+  pc = fma(pc, z, -2.75573143513906633035e-07);
+  pc = fma(pc, z, 2.48015872894767294178e-05);
+  pc = fma(pc, z, -1.38888888888741095749e-03);
+  pc = fma(pc, z, 4.16666666666666019037e-02);
+  const double cr = fma(z * z, pc, fma(-0.5, z, 1.0));
+  const double a = (q & 1) ? cr : sr, b = (q & 1) ? sr : cr;
+  *s = (q & 2) ? -a : a;
+  *c = ((q + 1) & 2) ? -b : b;
+}
+
 // 3x3 row-major
 struct M3 {
   double m[9];

@@ -50,7 +50,12 @@ def test_mpc_steps_match_the_oracle(built_library, name):
             xs, us = shift_reference(np.array(s.xs), np.array(s.us), x_meas[b])
             problem.x0 = x_meas[b].copy()
             s.solve(list(xs), list(us), step_iters)
-            assert U.rel_err(mpc.solver.t["xs"][b].cpu().numpy(), np.array(s.xs)) <= 1e-8, (step, b)
-            assert U.rel_err(mpc.solver.t["us"][b].cpu().numpy(), np.array(s.us)) <= 1e-8, (step, b)
-            assert U.rel_err(u0[b], np.array(s.us[0])) <= 1e-8
+            # An MPC step stops after `step_iters` iterations, far from convergence: what is compared is an
+            # intermediate iterate, on which rounding differences of the previous steps are amplified (the 7-link arm
+            # by ~2.3x per iteration, tests/test_host_math.py: check_chain7_T200; measured here 1.3e-8 on us after
+            # 6 + 2 x 3 iterations with a 1-ulp different sin / cos).  2-DOF arm: 1e-8; 7-link arm: 1e-7.
+            tol = 1e-8 if name == "sea" else 1e-7
+            assert U.rel_err(mpc.solver.t["xs"][b].cpu().numpy(), np.array(s.xs)) <= tol, (step, b)
+            assert U.rel_err(mpc.solver.t["us"][b].cpu().numpy(), np.array(s.us)) <= tol, (step, b)
+            assert U.rel_err(u0[b], np.array(s.us[0])) <= tol
             assert abs(st["cost"][b] - s.cost) <= 1e-8 * max(1.0, abs(s.cost))
