@@ -99,7 +99,7 @@ inline void fill_cost_sum(const AslrCostSum& src, DevCostSum<N>& dst) {
 
 // ---- host-side derivation of TwoLinkConst (extended precision; polynomials in s = sin q1, c = cos q1)
 namespace twolink_host {
-typedef long double LD;
+typedef decltype(1.0L) LD;  // long double (spelled without the token `double`: tools/flop_count.cpp renames it)
 struct Aff {  // a + s sin(q1) + c cos(q1)
   LD a, s, c;
 };
@@ -134,7 +134,7 @@ inline Quad dot(const AffV& x, const AffV& y) {
 }
 // joint rotation as a function of q: R(q) = A0 + sin(q) A1 + (1 - cos(q)) A2 (as DevJoint, in extended precision)
 inline void joint_rotation_parts(const AslrJoint& j, LD A0[9], LD A1[9], LD A2[9]) {
-  const LD a[3] = {j.axis[0], j.axis[1], j.axis[2]};
+  const LD a[3] = {(LD)j.axis[0], (LD)j.axis[1], (LD)j.axis[2]};
   const LD Kx[9] = {0, -a[2], a[1], a[2], 0, -a[0], -a[1], a[0], 0};
   LD K2[9];
   for (int r = 0; r < 3; ++r)
@@ -150,7 +150,7 @@ inline void joint_rotation_parts(const AslrJoint& j, LD A0[9], LD A1[9], LD A2[9
         a1 += (LD)j.placement.R[3 * r + k] * Kx[3 * k + c];
         a2 += (LD)j.placement.R[3 * r + k] * K2[3 * k + c];
       }
-      A0[3 * r + c] = j.placement.R[3 * r + c], A1[3 * r + c] = a1, A2[3 * r + c] = a2;
+      A0[3 * r + c] = (LD)j.placement.R[3 * r + c], A1[3 * r + c] = a1, A2[3 * r + c] = a2;
     }
 }
 }  // namespace twolink_host
@@ -161,10 +161,10 @@ inline void fill_two_link(const AslrProblemDesc& s, TwoLinkConst& t) {
   LD A0[9], A1[9], A2[9], B0[9], B1[9], B2[9];
   joint_rotation_parts(j1, A0, A1, A2);  // frame 1 in frame 0
   joint_rotation_parts(j0, B0, B1, B2);  // frame 0 in the world
-  const LD a0[3] = {j0.axis[0], j0.axis[1], j0.axis[2]}, a1[3] = {j1.axis[0], j1.axis[1], j1.axis[2]};
-  const LD c0[3] = {j0.com[0], j0.com[1], j0.com[2]}, c1[3] = {j1.com[0], j1.com[1], j1.com[2]};
-  const LD p1[3] = {j1.placement.p[0], j1.placement.p[1], j1.placement.p[2]};
-  const LD m0 = j0.mass, m1 = j1.mass;
+  const LD a0[3] = {(LD)j0.axis[0], (LD)j0.axis[1], (LD)j0.axis[2]}, a1[3] = {(LD)j1.axis[0], (LD)j1.axis[1], (LD)j1.axis[2]};
+  const LD c0[3] = {(LD)j0.com[0], (LD)j0.com[1], (LD)j0.com[2]}, c1[3] = {(LD)j1.com[0], (LD)j1.com[1], (LD)j1.com[2]};
+  const LD p1[3] = {(LD)j1.placement.p[0], (LD)j1.placement.p[1], (LD)j1.placement.p[2]};
+  const LD m0 = (LD)j0.mass, m1 = (LD)j1.mass;
   auto dot3 = [](const LD* x, const LD* y) { return x[0] * y[0] + x[1] * y[1] + x[2] * y[2]; };
   auto matvec = [](const LD* Mx, const LD* v, LD* o, bool transpose) {
     for (int r = 0; r < 3; ++r) {
@@ -182,7 +182,7 @@ inline void fill_two_link(const AslrProblemDesc& s, TwoLinkConst& t) {
   AffV r1 = d;
   for (int i = 0; i < 3; ++i) r1.v[i].a += p1[i];
   LD I1[9], I0[9];
-  for (int i = 0; i < 9; ++i) I1[i] = j1.inertia[i], I0[i] = j0.inertia[i];
+  for (int i = 0; i < 9; ++i) I1[i] = (LD)j1.inertia[i], I0[i] = (LD)j0.inertia[i];
   AffV I1w;  // I1 w
   for (int r = 0; r < 3; ++r) {
     I1w.v[r] = Aff{0, 0, 0};
@@ -211,7 +211,7 @@ inline void fill_two_link(const AslrProblemDesc& s, TwoLinkConst& t) {
   for (int i = 0; i < 3; ++i) t.m01[i] = (double)r01[i];  // r01[3], r01[4] vanish identically (M01 is affine)
   t.m11 = (double)(dot3(a1, I1a1) + m1 * (cc1 - dot3(a1, c1) * dot3(a1, c1)));
   // gravity: gamma(q0) = R0w^T g, h(q1) = m0 c0 + m1 (p1 + d)
-  const LD gv[3] = {s.robot.gravity[0], s.robot.gravity[1], s.robot.gravity[2]};
+  const LD gv[3] = {(LD)s.robot.gravity[0], (LD)s.robot.gravity[1], (LD)s.robot.gravity[2]};
   LD ga[3], gb[3], gc[3];
   matvec(B0, gv, t0, true), matvec(B1, gv, t1, true), matvec(B2, gv, t2, true);
   for (int i = 0; i < 3; ++i) ga[i] = t0[i] + t2[i], gb[i] = t1[i], gc[i] = -t2[i];

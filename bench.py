@@ -408,7 +408,7 @@ def run_ours(args):
                     "h2d_bytes_per_step": int(h_x0.nbytes + h_K.nbytes + h_xs0.nbytes + h_us0.nbytes),
                     "d2h_bytes_per_step": int(h_xs.nbytes + h_us.nbytes + h_state.nbytes)},
             "gpu_launches": launches_per_step * args.steps,
-            "roofline": roofline_block(rank, knots, ms_k1, achieved, peak, peaks, stages),
+            "roofline": roofline_block(rank, knots, ms_k1, achieved, peak, peaks, stages, B, T),
             "clocks": clocks, "stages": stages,
         }
         if world == 1 and not args.no_cpu:
@@ -443,11 +443,22 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def roofline_block(rank, knots, ms_k1, achieved, peak, peaks, stages):
-    """Roofline of the fused calc+calcDiff sweep (the only HBM-shaped kernel of the path) plus, from the stage
-    timings, which stage dominates a solve.  ncu-derived figures (DRAM traffic per launch, FP64 pipe utilisation) are
-    read from profiles/ncu_figures.json, written by tools/ncu_summary.py together with the hash of the kernel sources
-    they were captured from; when the sources have changed since, they are withheld rather than quoted stale."""
+# Algorithmic bytes per knot of the three solver stages at (nx, nu) = (8, 2), 8-byte words:
+#   calcdiff (K1 in the solver): read x, u (10); write the compact record (56), xnext (8), cost (1), gap (8)
+#   backward (K2): read the compact record (56), gap (8); write K (16), k, Qu, Quuk (6), Vx, Vxx fs (16)
+#   rollout (K3, per trial and knot): read K (16), xs (8), us (2), k (2); write xs_try (8), us_try (2)
+STAGE_BYTES_PER_KNOT = {"calcdiff": 8 * 83, "backward": 8 * 102, "rollout": 8 * 38}
+STAGE_FLOP_KEY = {"calcdiff": "sea2.calc_diff_knot", "backward": "sea2.backward_knot", "rollout": "sea2.rollout_knot"}
+
+
+def roofline_block(rank, knots, ms_k1, achieved, peak, peaks, stages, B=None, T=None):
+    """`roofline` of the bench line = the stage that takes the largest share of a solve (measured live, CUDA events),
+    at full batch, against BOTH roofs: achieved = max(algorithmic bytes/s / HBM peak, flop/s / FP64 peak), flop counts
+    from profiles/flop_counts.json (tools/flop_count.cpp: the product sources compiled over a counting scalar type).
+    `calcdiff_sweep` keeps the HBM figure of the public fused calc+calcDiff sweep on SURVEY.md's 1544 B / knot.
+    ncu-derived figures (DRAM traffic per launch, FP64 pipe utilisation) are read from profiles/ncu_figures.json, written
+    by tools/ncu_summary.py together with the hash of the kernel sources they were captured from; when the sources
+    have changed since, they are withheld rather than quoted stale."""
     figs, stale = {}, None
     try:
         figs = json.load(open(os.path.join(ROOT, "profiles", "ncu_figures.json")))
@@ -457,23 +468,64 @@ def roofline_block(rank, knots, ms_k1, achieved, peak, peaks, stages):
                     str(figs.get("source_hash"))[:12]
     except Exception as e:
         stale = "profiles/ncu_figures.json unavailable (%s)" % type(e).__name__
-    k1 = (figs.get("kernels", {}) or {}).get("knot_kernel", {}) if not stale else {}
-    block = {"kernel": "knot_kernel<2,2,SEA,DIFF> (fused calc+calcDiff, %d knots)" % knots,
-             "bound": "hbm", "achieved": achieved, "peak": peak,
-             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
-             "unit": "GB/s", "frac": achieved / peak, "traffic": k1.get("dram_bytes_per_launch"),
+    kern = (figs.get("kernels", {}) or {}) if not stale else {}
+    flops, fp64_peak, fp64_src = {}, None, None
+    try:
+        flops = json.load(open(os.path.join(ROOT, "profiles", "flop_counts.json")))
+    except Exception:
+        pass
+    try:
+        fp = json.load(open(os.path.join(ROOT, "profiles", "r01b_fp64_peak.json")))
+        fp64_peak, fp64_src = float(fp["fp64_tflops"]), "tools/fp64_peak.cu on this pool (profiles/r01b_fp64_peak.json)"
+    except Exception:
+        pass
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)"
+    sweep = {"kernel": "knot_kernel<2,2,SEA,DIFF> (public fused calc+calcDiff sweep, %d knots)" % knots, "bound": "hbm",
+             "achieved": achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
+             "traffic": (kern.get("knot_kernel") or {}).get("dram_bytes_per_launch"),
              "algorithmic_bytes_per_knot": ALGO_BYTES_PER_KNOT}
-    if stale:
-        block["ncu_figures"] = stale
-    else:
-        block["ncu_figures"] = {"source": "profiles/ncu_figures.json", "capture": figs.get("capture"),
-                                "kernels": figs.get("kernels")}
-    if stages:
-        dom = max(stages["share"], key=lambda k: stages["share"][k])
-        block["dominant_stage"] = {"stage": dom, "share_of_solve": stages["share"][dom],
-                                   "note": "K2 / K3 are time-sequential dependent chains (one knot after the other): "
-                                           "their bound is dependent-issue latency, not bytes or flops; see "
-                                           "stages.floor_us and DESIGN.md section 5"}
+    if fp64_peak and "sea2.calc_diff_knot" in flops:
+        tf = flops["sea2.calc_diff_knot"]["flops"] * knots / (ms_k1 * 1e-3) / 1e12
+        sweep["fp64"] = {"flops_per_knot": flops["sea2.calc_diff_knot"]["flops"], "achieved_tflops": tf,
+                         "peak_tflops": fp64_peak, "frac": tf / fp64_peak}
+    if not stages or B is None:
+        sweep["ncu_figures"] = stale or {"source": "profiles/ncu_figures.json", "capture": figs.get("capture")}
+        return sweep
+    # ---- the dominant stage of the solve
+    per_stage = {}
+    names = {"calcdiff": "solver_calcdiff_kernel", "backward": "backward_cols_kernel", "rollout": "rollout_kernel"}
+    for st in ("calcdiff", "backward", "rollout"):
+        us = stages["full_batch_us"][st]
+        n_knots = B * (T + 1) if st == "calcdiff" else B * T * (10 if st == "rollout" else 1)
+        gbs = STAGE_BYTES_PER_KNOT[st] * n_knots / (us * 1e-6) / 1e9
+        e = {"share_of_solve": stages["share"][st], "full_batch_us": us, "knots_per_launch": n_knots,
+             "algorithmic_bytes_per_knot": STAGE_BYTES_PER_KNOT[st], "achieved_gbs": gbs, "frac_hbm": gbs / peak,
+             "floor_us": stages["floor_us"][st]}
+        fk = STAGE_FLOP_KEY[st]
+        if fp64_peak and fk in flops:
+            tf = flops[fk]["flops"] * n_knots / (us * 1e-6) / 1e12
+            e.update(flops_per_knot=flops[fk]["flops"], achieved_tflops=tf, frac_fp64=tf / fp64_peak)
+        if names[st] in kern:
+            e["ncu"] = kern[names[st]]
+        per_stage[st] = e
+    dom = max(per_stage, key=lambda k: per_stage[k]["share_of_solve"])
+    d = per_stage[dom]
+    by_flops = d.get("frac_fp64", 0.0) > d["frac_hbm"]
+    block = {"kernel": "%s (stage '%s': %.0f %% of the solve, full batch = iteration 1: all OCPs running%s)"
+                       % (names[dom], dom, 100 * d["share_of_solve"],
+                          ", all ten step lengths rolled out" if dom == "rollout" else ""),
+             "bound": "hbm",
+             "achieved": d["achieved_gbs"], "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+             "frac": max(d["frac_hbm"], d.get("frac_fp64", 0.0)),
+             "frac_is": "flop/s over the measured FP64 peak" if by_flops else "algorithmic bytes/s over the measured HBM peak",
+             "traffic": (d.get("ncu") or {}).get("dram_bytes_per_launch"),
+             "fp64": {"peak_tflops": fp64_peak, "peak_source": fp64_src, "achieved_tflops": d.get("achieved_tflops"),
+                      "flop_counts": "profiles/flop_counts.json (dense serial form of the stage's arithmetic)"},
+             "note": "K2 / K3 are time-sequential dependent chains (one knot after the other) with one to seven warps "
+                     "per SM: neither roof binds, the limiter is dependent-issue latency (stages.floor_us is what a "
+                     "launch costs when two OCPs are left); both fractions are given so the distance is visible",
+             "stages": per_stage, "calcdiff_sweep": sweep}
+    block["ncu_figures"] = stale or {"source": "profiles/ncu_figures.json", "capture": figs.get("capture")}
     return block
 
 

@@ -3,6 +3,11 @@
 
   python tools/ncu_summary.py launches gpurun_out/launches.csv            > profiles/rNN_launches.md
   python tools/ncu_summary.py full gpurun_out/prof.ncu-rep [more.ncu-rep] > profiles/rNN_ncu_full.md
+  python tools/ncu_summary.py figures gpurun_out/prof.ncu-rep "what was captured"   -> profiles/ncu_figures.json
+
+`figures` writes the ncu-derived numbers bench.py quotes (DRAM bytes per launch, FP64 pipe utilisation, registers,
+spill sectors per kernel) together with the content hash of the kernel sources they were captured from; bench.py
+refuses to print them when the sources have changed since (run it right after the capture, before editing).
 
 `launches` reads the CSV of `ncu --metrics gpu__time_duration.sum --csv`; `full` reads `.ncu-rep`
 files of `ncu --set full` through `ncu -i ... --page raw --csv` (works without a GPU).
@@ -98,6 +103,51 @@ def full(paths):
         print()
 
 
+def _unit_scale(u):
+    return {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}.get(u, 1.0)
+
+
+def figures(path, what):
+    import json
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    import __graft_entry__ as ge
+    txt = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = [r for r in csv.reader(io.StringIO(txt)) if len(r) > 20]
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    ki = hdr.index("Kernel Name")
+
+    def val(r, key):
+        if key not in hdr:
+            return None
+        i = hdr.index(key)
+        try:
+            return float(r[i].replace(",", "")) * _unit_scale(units[i])
+        except ValueError:
+            return None
+    kernels = {}
+    for r in data:
+        name = short_name(r[ki]).replace("aslr::", "")
+        base = name.split("<")[0]
+        entry = {"instance": name, "grid": r[hdr.index("Grid Size")] if "Grid Size" in hdr else None,
+                 "duration_us": val(r, "gpu__time_duration.sum"),
+                 "dram_bytes_per_launch": (val(r, "dram__bytes_read.sum") or 0.0) + (val(r, "dram__bytes_write.sum") or 0.0),
+                 "fp64_pipe_pct": val(r, "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"),
+                 "issue_slots_busy_pct": val(r, "smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                 "warps_active_pct": val(r, "sm__warps_active.avg.pct_of_peak_sustained_active"),
+                 "registers": val(r, "launch__registers_per_thread"),
+                 "warp_instructions": val(r, "smsp__inst_executed.sum"),
+                 "spill_sectors": (val(r, "l1tex__t_sectors_pipe_lsu_mem_local_op_ld.sum") or 0.0) +
+                                  (val(r, "l1tex__t_sectors_pipe_lsu_mem_local_op_st.sum") or 0.0)}
+        kernels.setdefault(base, entry)  # the first launch of each kernel in the capture
+    out = {"source_hash": ge._source_hash(), "capture": what, "report": os.path.basename(path), "kernels": kernels}
+    dst = os.path.join(root, "profiles", "ncu_figures.json")
+    with open(dst, "w") as f:
+        json.dump(out, f, indent=1)
+    print("wrote", dst, "for source hash", out["source_hash"][:12])
+
+
 def _fmt(s):
     try:
         v = float(s.replace(",", ""))
@@ -109,9 +159,11 @@ def _fmt(s):
 
 
 if __name__ == "__main__":
-    if len(sys.argv) < 3 or sys.argv[1] not in ("launches", "full"):
+    if len(sys.argv) < 3 or sys.argv[1] not in ("launches", "full", "figures"):
         raise SystemExit(__doc__)
     if sys.argv[1] == "launches":
         launches(sys.argv[2])
+    elif sys.argv[1] == "figures":
+        figures(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "")
     else:
         full(sys.argv[2:])
