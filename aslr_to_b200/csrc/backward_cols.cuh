@@ -36,7 +36,7 @@ struct ColsSmem {
   static constexpr int RSZ = CRec<NX / 4, NU>::SIZE;  // the compact K1 -> K2 record (knot.cuh), double-buffered
   static constexpr int REC0 = 0;
   static constexpr int REC1 = RSZ;
-  static constexpr int FXF = 2 * RSZ;         // Fx of the current knot, rebuilt from a_x (row j by lane j)
+  static constexpr int FXF = 2 * RSZ;         // W = dt V'[0:2n,:] + V'[2n:,:] (2n x NX) of the current knot
   static constexpr int VXX = FXF + NX * NX;
   static constexpr int VT = VXX + NX * NX;
   static constexpr int KG = VT + NX * NX;
@@ -236,6 +236,8 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
     }
     sts_row<NX>(sm + CS::VXX + j * NX, vrow);
     sm[CS::VX + j] = vx;
+#pragma unroll
+    for (int k = 0; k < 2 * NQ; ++k) sm[CS::FXF + k * NX + j] = fma(dt, vrow[k], vrow[2 * NQ + k]);  // column j of W
   }
   cp_async_drain();
   g.sync();
@@ -263,104 +265,120 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
       for (int k = 0; k < NX; ++k) fsv[k] = fs[t * NX + k];
       fsj = fs[t * NX + j];
     }
-    // ---- Fx = I + dt [[dt a_x + [0 I]], [a_x]] (integrated_action.py:33-35): lane j rebuilds row j from row
-    // j mod 2n of a_x with the expression record_put uses, and parks it in shared memory (every product below
-    // takes whole rows of Fx as broadcast operands, and lane j needs column j)
-    const int jr = (j < 2 * NQ) ? j : j - 2 * NQ;  // the row of a_x / a_u behind row j of Fx / Fu
-    const double jsc = (j < 2 * NQ) ? dt2 : dt;
-    {
-      double ax[3 * NQ], fr[NX];
-      if constexpr ((3 * NQ) % 2 == 0) {
-        lds_row<3 * NQ>(R + RC::AX + jr * 3 * NQ, ax);
-      } else {
+    // ---- The discrete Jacobians are never formed.  With H = 2n, a_x = d[a_l; a_m]/dx (H x NX, v_m columns zero),
+    // S = [0 I] (H x NX) and a_u (H x NU), integrated_action.py:33-37 gives
+    //     Fx = I + E,   E = [dt^2 a_x + dt S ; dt a_x],   Fu = [dt^2 a_u ; dt a_u],
+    // so every product with Fx / Fu collapses onto the H rows of a_x / a_u:
+    //     Fx^T V' = V' + dt (a_x^T W + S^T V'[0:H,:]),        W  = dt V'[0:H,:] + V'[H:,:]      (H x NX)
+    //     A Fx    = A + a2 a_x + dt [0 | A[:,0:H]],            a2 = dt (dt A[:,0:H] + A[:,H:])   (per row: H values)
+    //     A Fu    = a2 a_u,        Fu^T V' = dt a_u^T W,        Fx^T Vx' = Vx' + dt (a_x^T wv + S^T Vx'[0:H]),
+    //     Fu^T Vx' = dt a_u^T wv,  wv = dt Vx'[0:H] + Vx'[H:]
+    // -- half the multiply-adds and shared-memory operand loads of the dense products (which skipped the exact
+    // zeros of Fx one by one), and no NX x NX matrix to rebuild per knot.  Lane j holds row j of V', so by the exact
+    // symmetry of V' it also holds column j of W (w2 below); the rows of W were parked in shared memory by the
+    // previous knot.
+    constexpr int H = 2 * NQ;
+    const double* WS = sm + CS::FXF;  // W rows (H x NX), written with V'
+    const bool lo = j < H;            // rows q of Fx / Fu (dt^2 a + ...) vs rows v (dt a)
+    const int jr = lo ? j : j - H;    // the row of a_x / a_u behind row j of Fx / Fu
+    const double jsc = lo ? dt2 : dt;
+    // column j of a_x (zero for the v_m columns) and all of a_u
+    double axc[H];
 #pragma unroll
-        for (int c = 0; c < 3 * NQ; ++c) ax[c] = R[RC::AX + jr * 3 * NQ + c];
-      }
+    for (int k = 0; k < H; ++k) axc[k] = (j < 3 * NQ) ? R[RC::AX + k * 3 * NQ + (j < 3 * NQ ? j : 0)] : 0.0;
+    double au[H][NU];
 #pragma unroll
-      for (int c = 0; c < NX; ++c) {
-        const double a_ = (c < 3 * NQ) ? ax[c < 3 * NQ ? c : 0] : 0.0;
-        fr[c] = fma(jsc, a_, (c == j) ? 1.0 : 0.0) + ((j < 2 * NQ && c == j + 2 * NQ) ? dt : 0.0);
-      }
-      sts_row<NX>(sm + CS::FXF + j * NX, fr);
-    }
-    // Fu = [dt^2 a_u; dt a_u] (integrated_action.py:36-37): all of it in registers
-    double fu[NX][NU];
-#pragma unroll
-    for (int k = 0; k < NX; ++k) {
+    for (int k = 0; k < H; ++k) {
       if (!fu_nonzero<NX, NU>(k)) {
 #pragma unroll
-        for (int i = 0; i < NU; ++i) fu[k][i] = 0.0;
+        for (int i = 0; i < NU; ++i) au[k][i] = 0.0;
+      } else if constexpr (NU % 2 == 0) {
+        double r[NU];
+        lds_row<NU>(R + RC::AU + k * NU, r);
+#pragma unroll
+        for (int i = 0; i < NU; ++i) au[k][i] = r[i];
       } else {
-        const int kr = (k < 2 * NQ) ? k : k - 2 * NQ;
-        const double ksc = (k < 2 * NQ) ? dt2 : dt;
-        if constexpr (NU % 2 == 0) {
-          double r[NU];
-          lds_row<NU>(R + RC::AU + kr * NU, r);
 #pragma unroll
-          for (int i = 0; i < NU; ++i) fu[k][i] = ksc * r[i];
-        } else {
-#pragma unroll
-          for (int i = 0; i < NU; ++i) fu[k][i] = ksc * R[RC::AU + kr * NU + i];
-        }
+        for (int i = 0; i < NU; ++i) au[k][i] = R[RC::AU + k * NU + i];
       }
     }
-    g.sync();  // rows of Fx are in place
-    const double* FX = sm + CS::FXF;
-    double fxc[NX];  // column j of Fx
-#pragma unroll
-    for (int k = 0; k < NX; ++k) fxc[k] = FX[k * NX + j];
-    // ---- A[j,:] = sum_k Fx[k][j] Vxx'[k,:]
+    // ---- A[j,:] = (Fx^T V')[j,:]
     double arow[NX];
-#pragma unroll
-    for (int c = 0; c < NX; ++c) arow[c] = 0.0;
-#pragma unroll
-    for (int k = 0; k < NX; ++k) {
-      double v[NX];
-      lds_row<NX>(sm + CS::VXX + k * NX, v);
-#pragma unroll
-      for (int c = 0; c < NX; ++c) arow[c] += fxc[k] * v[c];
-    }
-    // ---- FuV[:,j] = sum_k Fu[k][:] Vxx'[k][j]  (Vxx'[k][j] = Vxx'[j][k], the lane's own row)
-    double fuv[NU];
-#pragma unroll
-    for (int i = 0; i < NU; ++i) {
-      double s = 0.0;
-#pragma unroll
-      for (int k = 0; k < NX; ++k)
-        if (fu_nonzero<NX, NU>(k)) s += fu[k][i] * vrow[k];
-      fuv[i] = s;
-    }
-    // ---- Qx[j] = Lx[j] + Fx[:,j]^T Vx', Qu = Lu + Fu^T Vx' (every lane)
-    double qx, qu[NU];
-    {
-      double vxa[NX];
-      lds_row<NX>(sm + CS::VX, vxa);
-      double s = 0.0;
-#pragma unroll
-      for (int k = 0; k < NX; ++k) s += fxc[k] * vxa[k];
-      qx = R[RC::LX + j] + s;
-#pragma unroll
-      for (int i = 0; i < NU; ++i) {
-        double s2 = 0.0;
-#pragma unroll
-        for (int k = 0; k < NX; ++k)
-          if (fu_nonzero<NX, NU>(k)) s2 += fu[k][i] * vxa[k];
-        qu[i] = R[RC::LU + i] + s2;
-      }
-    }
-    // ---- Qxx[j,:] = Lxx[j,:] + A[j,:] Fx, Qxu[j,:] = Lxu[j,:] + A[j,:] Fu
-    double qxx[NX], qxu[NU];
     {
       double s[NX];
 #pragma unroll
       for (int c = 0; c < NX; ++c) s[c] = 0.0;
 #pragma unroll
-      for (int k = 0; k < NX; ++k) {
-        double f[NX];
-        lds_row<NX>(FX + k * NX, f);
+      for (int k = 0; k < H; ++k) {
+        double w[NX];
+        lds_row<NX>(WS + k * NX, w);
 #pragma unroll
-        for (int c = 0; c < NX; ++c)
-          if (fx_nonzero<NX>(k, c)) s[c] += arow[k] * f[c];
+        for (int c = 0; c < NX; ++c) s[c] += axc[k] * w[c];
+      }
+      double v[NX];
+      lds_row<NX>(sm + CS::VXX + jr * NX, v);  // row j - H of V' for the v rows (S^T V'); unused by the q rows
+#pragma unroll
+      for (int c = 0; c < NX; ++c) arow[c] = fma(dt, lo ? s[c] : s[c] + v[c], vrow[c]);
+    }
+    // ---- wv, Qx[j] = Lx[j] + (Fx^T Vx')[j], Qu = Lu + Fu^T Vx' (every lane)
+    double qx, qu[NU];
+    {
+      double vxa[NX], wv[H];
+      lds_row<NX>(sm + CS::VX, vxa);
+#pragma unroll
+      for (int k = 0; k < H; ++k) wv[k] = fma(dt, vxa[k], vxa[H + k]);
+      double s = 0.0;
+#pragma unroll
+      for (int k = 0; k < H; ++k) s += axc[k] * wv[k];
+      double vxs = 0.0;  // Vx'[j - H] for the v rows
+#pragma unroll
+      for (int k = 0; k < H; ++k)
+        if (k == jr) vxs = vxa[k];
+      qx = R[RC::LX + j] + fma(dt, lo ? s : s + vxs, vx);
+#pragma unroll
+      for (int i = 0; i < NU; ++i) {
+        double s2 = 0.0;
+#pragma unroll
+        for (int k = 0; k < H; ++k)
+          if (fu_nonzero<NX, NU>(k)) s2 += au[k][i] * wv[k];
+        qu[i] = fma(dt, s2, R[RC::LU + i]);
+      }
+    }
+    // ---- FuV[:,j] = (Fu^T V')[:,j] = dt a_u^T W[:,j],  W[:,j] = dt V'[j,0:H] + V'[j,H:] (own row, by symmetry)
+    double fuv[NU];
+    {
+      double w2[H];
+#pragma unroll
+      for (int k = 0; k < H; ++k) w2[k] = fma(dt, vrow[k], vrow[H + k]);
+#pragma unroll
+      for (int i = 0; i < NU; ++i) {
+        double s = 0.0;
+#pragma unroll
+        for (int k = 0; k < H; ++k)
+          if (fu_nonzero<NX, NU>(k)) s += au[k][i] * w2[k];
+        fuv[i] = dt * s;
+      }
+    }
+    // ---- Qxx[j,:] = Lxx[j,:] + (A Fx)[j,:], Qxu[j,:] = (A Fu)[j,:]   (Lxu = 0: no cost of the menu couples x and u)
+    double qxx[NX], qxu[NU];
+    {
+      double a2[H];
+#pragma unroll
+      for (int k = 0; k < H; ++k) a2[k] = dt * fma(dt, arow[k], arow[H + k]);
+      double s[3 * NQ];
+#pragma unroll
+      for (int c = 0; c < 3 * NQ; ++c) s[c] = 0.0;
+#pragma unroll
+      for (int k = 0; k < H; ++k) {
+        double ar[3 * NQ];
+        if constexpr ((3 * NQ) % 2 == 0) {
+          lds_row<3 * NQ>(R + RC::AX + k * 3 * NQ, ar);
+        } else {
+#pragma unroll
+          for (int c = 0; c < 3 * NQ; ++c) ar[c] = R[RC::AX + k * 3 * NQ + c];
+        }
+#pragma unroll
+        for (int c = 0; c < 3 * NQ; ++c) s[c] += a2[k] * ar[c];
       }
       // row j of Lxx = diagonal part + the (q_l, q_l) block of the placement cost (record_put)
       const double lxxd = R[RC::LXXD + j];
@@ -368,15 +386,17 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
       for (int c = 0; c < NX; ++c) {
         double l = (c == j) ? lxxd : 0.0;
         if (c < NQ) l += (j < NQ) ? R[RC::LQQ + (j < NQ ? j : 0) * NQ + c] : 0.0;
-        qxx[c] = l + s[c];
+        double q = arow[c] + ((c < 3 * NQ) ? s[c < 3 * NQ ? c : 0] : 0.0);
+        if (c >= H) q = fma(dt, arow[c >= H ? c - H : 0], q);
+        qxx[c] = l + q;
       }
 #pragma unroll
       for (int i = 0; i < NU; ++i) {
         double s2 = 0.0;
 #pragma unroll
-        for (int k = 0; k < NX; ++k)
-          if (fu_nonzero<NX, NU>(k)) s2 += arow[k] * fu[k][i];
-        qxu[i] = 0.0 + s2;  // Lxu = 0: no cost of the menu couples x and u
+        for (int k = 0; k < H; ++k)
+          if (fu_nonzero<NX, NU>(k)) s2 += a2[k] * au[k][i];
+        qxu[i] = s2;
       }
     }
     // ---- Quu = Luu + (FuV Fu + ureg I): butterfly sum of the lanes' terms FuV[:,j] Fu[j,:]
@@ -495,9 +515,11 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
       for (int c = 0; c < NX; ++c) bad = bad || isnan(vrow[c]) || bad_value(fabs(vrow[c]));
       if ((__ballot_sync(ASLR_FULL, bad) & mask) != 0u && live) failed = true, live = false;
     }
-    // ---- the next knot reads Vxx, Vx from shared memory (safe: every lane is past its reads of them)
+    // ---- the next knot reads Vxx, Vx and W from shared memory (safe: every lane is past its reads of them)
     sts_row<NX>(sm + CS::VXX + j * NX, vrow);
     sm[CS::VX + j] = vx;
+#pragma unroll
+    for (int k = 0; k < 2 * NQ; ++k) sm[CS::FXF + k * NX + j] = fma(dt, vrow[k], vrow[2 * NQ + k]);  // column j of W
     // ---- store (the pointers walk backwards with t)
     if (live) {
 #pragma unroll
