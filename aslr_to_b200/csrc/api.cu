@@ -60,11 +60,13 @@ int launch_accept(const SolverArgs& a, cudaStream_t s) {
 // aslr_solve); counters[k] is the "still running" word of sub-batch k (layout of AslrSolverBuffers.counters: make_args)
 #define ASLR_MAX_LANES 8
 #ifndef ASLR_SOLVE_LANES
-#define ASLR_SOLVE_LANES 4
+#define ASLR_SOLVE_LANES 2  // measured on the 4096-OCP 2-DOF batch, round 2 kernels: 1 lane 34.9 ms, 2 lanes 34.5,
+                            // 4 lanes 35.7, 6 lanes 36.3, 8 lanes 38.4 (round 1 kernels: 4 lanes 59.2 -> 56.8 ms).
+                            // The shorter the per-knot chains, the less a second stream finds to fill
 #endif
 #ifndef ASLR_LANE_MIN_OCPS
-#define ASLR_LANE_MIN_OCPS 1024  // smallest sub-batch worth a stream of its own (measured: 4 x 1024 OCPs of the
-                                 // 2-DOF batch 59.2 -> 56.8 ms; 4 x 256 OCPs of the 7-DOF batch 83.8 -> 84.8 ms)
+#define ASLR_LANE_MIN_OCPS 1024  // smallest sub-batch worth a stream of its own (4 x 256 OCPs of the 7-DOF batch:
+                                 // 83.8 -> 84.8 ms)
 #endif
 
 struct AslrProblem {

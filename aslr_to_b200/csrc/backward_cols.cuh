@@ -587,8 +587,26 @@ __device__ void backward_body_cols(const GrpCols<NX>& g, double* sm, const Solve
   if (__any_sync(ASLR_FULL, rc)) {
     double c = 0.0, ff = 0.0;
     if (rc) {
-      for (int t = g.lane; t <= T; t += G) c += a.buf.knot_cost[(size_t)b * (T + 1) + t];
-      for (int e = g.lane; e < (T + 1) * NX; e += G) ff = fmax(ff, fabs(a.buf.fs[(size_t)b * (T + 1) * NX + e]));
+      // loads four at a time (they do not depend on each other; one at a time every addition waited for L2);
+      // the additions keep their order
+      const double* kc = a.buf.knot_cost + (size_t)b * (T + 1);
+      int t = g.lane;
+      for (; t + 3 * G <= T; t += 4 * G) {
+        const double c0 = kc[t], c1 = kc[t + G], c2 = kc[t + 2 * G], c3 = kc[t + 3 * G];
+        c += c0, c += c1, c += c2, c += c3;
+      }
+      for (; t <= T; t += G) c += kc[t];
+      if (!st.is_feasible) {  // (a feasible OCP reports ffeas = 0 whatever the stored gaps are)
+        const double* fsb = a.buf.fs + (size_t)b * (T + 1) * NX;
+        const int n = (T + 1) * NX;
+        int e = g.lane;
+        for (; e + 7 * G < n; e += 8 * G) {
+          double m0 = fmax(fabs(fsb[e]), fabs(fsb[e + G])), m1 = fmax(fabs(fsb[e + 2 * G]), fabs(fsb[e + 3 * G]));
+          double m2 = fmax(fabs(fsb[e + 4 * G]), fabs(fsb[e + 5 * G])), m3 = fmax(fabs(fsb[e + 6 * G]), fabs(fsb[e + 7 * G]));
+          ff = fmax(ff, fmax(fmax(m0, m1), fmax(m2, m3)));
+        }
+        for (; e < n; e += G) ff = fmax(ff, fabs(fsb[e]));
+      }
     }
     sm[SM::RED + g.lane] = c;
     sm[SM::RED + 128 + g.lane] = ff;
