@@ -68,7 +68,7 @@ struct KnotArgs {
 // both ways), and writes every record part back as contiguous 256-byte rows.
 template <int SIZE>
 struct RecParts {
-  static constexpr int NP = (SIZE + 63) / 64;
+  static constexpr int NP = (SIZE + 71) / 72;  // parts of <= 72 doubles (the compact records, 56 and 68, in one)
   static constexpr int LEN = ((SIZE + NP - 1) / NP + 1) & ~1;
   static constexpr int STRIDE = 33;
   static constexpr int WARP_DOUBLES = LEN * STRIDE;
@@ -126,6 +126,20 @@ __device__ __forceinline__ void staged_record(double* st, double* deriv, long g0
   }
 }
 
+// elements [LO, HI) of the dense record, staged and flushed in chunks of the stage's capacity
+template <int N, int NU, int LO, int HI>
+__device__ __forceinline__ void staged_range(double* st, double* deriv, long g0, unsigned mask, int lane, bool mine,
+                                             double dt, const KnotDeriv<N, NU>& kd) {
+  typedef Rec<4 * N, NU> RC;
+  typedef RecParts<RC::SIZE> RP;
+  if constexpr (LO < HI) {
+    constexpr int LEN = (HI - LO < RP::LEN) ? HI - LO : RP::LEN;
+    if (mine) record_put<N, NU, LO, LO + LEN>(st + lane - (size_t)LO * RP::STRIDE, RP::STRIDE, dt, kd);
+    flush_part<RC::SIZE, LO, LEN>(st, deriv, g0, mask, lane);
+    staged_range<N, NU, LO + LEN, HI>(st, deriv, g0, mask, lane, mine, dt, kd);
+  }
+}
+
 // stand-alone calc / calc+calcDiff sweep: one thread per knot (ShootingProblem.calc / calcDiff)
 template <int N, int NU, bool VSA, bool DIFF>
 __global__ void __launch_bounds__(128, (N <= 2) ? ASLR_K1_MINB : 1) knot_kernel(const __grid_constant__ DevProblem<N> P, const KnotArgs a) {
@@ -158,7 +172,26 @@ __global__ void __launch_bounds__(128, (N <= 2) ? ASLR_K1_MINB : 1) knot_kernel(
   double* dFx = (DIFF && a.out.dFx) ? a.out.dFx + (size_t)gc * 2 * N * NX : nullptr;
   double* dFu = (DIFF && a.out.dFu) ? a.out.dFu + (size_t)gc * 2 * N * NU : nullptr;
   const double dt = term ? P.dtT : P.dt;
-  if constexpr (STAGED) {
+  if constexpr (STAGED && TwoPhase<N>::value) {
+    // two-phase evaluation (knot.cuh: knot_costs_diff): dynamics half -> Fx | Fu staged and written, xnext out,
+    // then the cost half -> Lxx | Lxu | Luu | Lx | Lu
+    const int lane = threadIdx.x & 31;
+    const unsigned mask = __ballot_sync(0xffffffffu, live);
+    double* st = stage + (size_t)(threadIdx.x >> 5) * RecParts<RC::SIZE>::WARP_DOUBLES;
+    KnotDeriv<N, NU> kd;
+    if (live)
+      knot_core<N, NU, VSA, true, false>(P, term ? P.term : P.run, dt, x, u, Kocp, mref, xn, cost, kd, xout, dFx, dFu);
+    if (a.out.deriv) staged_range<N, NU, 0, RC::LXX>(st, a.out.deriv, g - lane, mask, lane, live, dt, kd);
+    if (live && a.out.xnext && !term) {
+      double* xo = a.out.xnext + ((size_t)b * a.T + t) * NX;
+#pragma unroll
+      for (int i = 0; i < NX; ++i) xo[i] = xn[i];
+    }
+    if (live) cost = knot_costs_diff<N, NU>(P, term ? P.term : P.run, x, u, mref, kd.acc);
+    if (a.out.deriv) staged_range<N, NU, RC::LXX, RC::SIZE>(st, a.out.deriv, g - lane, mask, lane, live, dt, kd);
+    if (live && a.out.cost) a.out.cost[g] = cost;
+    return;
+  } else if constexpr (STAGED) {
     KnotDeriv<N, NU> kd;
     if (live) knot_core<N, NU, VSA, true>(P, term ? P.term : P.run, dt, x, u, Kocp, mref, xn, cost, kd, xout, dFx, dFu);
     if (a.out.deriv) {
@@ -190,7 +223,19 @@ __global__ void __launch_bounds__(128, (N <= 2) ? ASLR_K1_MINB : 1) solver_calcd
   extern __shared__ double stage[];
   const long g = (long)blockIdx.x * blockDim.x + threadIdx.x;
   const long total = (long)a.B * (a.T + 1);
-  if constexpr (N <= ASLR_K1_STAGE_MAXN) {
+  if constexpr (COMPACT && TwoPhase<N>::value) {
+    // two-phase evaluation: the body parks both halves of the compact record in this thread's column of the
+    // warp's stage, the warp then writes its 32 records as contiguous rows
+    static_assert(RecParts<RSIZE>::NP == 1, "the compact record is staged in one piece");
+    const bool live = g < total;
+    const long gc = live ? g : total - 1;
+    const int lane = threadIdx.x & 31;
+    double* st = stage + (size_t)(threadIdx.x >> 5) * RecParts<RSIZE>::WARP_DOUBLES;
+    const bool wrote = calcdiff_body<N, NU, VSA, true>(P, a, (int)(gc / (a.T + 1)), (int)(gc % (a.T + 1)), live, nullptr,
+                                                       nullptr, st + lane, RecParts<RSIZE>::STRIDE);
+    const unsigned mask = __ballot_sync(0xffffffffu, wrote);
+    if (mask) flush_part<RSIZE, 0, RecParts<RSIZE>::LEN>(st, a.buf.deriv, g - lane, mask, lane);
+  } else if constexpr (N <= ASLR_K1_STAGE_MAXN) {
     const bool live = g < total;
     const long gc = live ? g : total - 1;
     KnotDeriv<N, NU> kd;

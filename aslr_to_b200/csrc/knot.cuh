@@ -697,6 +697,80 @@ ASLR_HD double knot_cost_only(const DevProblem<N>& P, const DevCostSum<N>& C, co
   return cost_terms<N, NU, false>(C, x, u, R, p, nullptr, mref, unused);
 }
 
+// Second phase of the two-phase knot evaluation (two-link models): forward kinematics + the cost sum WITH its
+// derivatives, nothing of the dynamics.  With the closed-form two-link terms the dynamics need no kinematics at all,
+// so calc + calcDiff splits into two halves that share only the state: knot_core<.., DIFF, COSTS = false> (a_x, a_u,
+// xnext) and this function (cost, Lx, Lu, Lxx, Luu).  Evaluated one after the other, each half's results parked in
+// the shared-memory stage before the other starts, the thread never holds both halves' 60 result doubles plus either
+// half's temporaries at once (the fused form needed 254 registers and still spilled).  The kinematics are the
+// statements of knot_core, so cost and derivatives are the same bits.
+template <int N, int NU>
+ASLR_HD double knot_costs_diff(const DevProblem<N>& P, const DevCostSum<N>& C, const double* x, const double* u,
+                               const double* mref, CostAcc<N>& acc) {
+  constexpr int NX = 4 * N;
+  M3 R[N];
+  V3 p[N];
+  SV S[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    double s, c;
+    joint_sincos(x[i], &s, &c);
+    const double omc = 1.0 - c;
+    M3 Rl;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) Rl.m[k] = P.j[i].A0[k] + s * P.j[i].A1[k] + omc * P.j[i].A2[k];
+    if (i == 0) {
+      R[0] = Rl;
+      p[0] = ld3(P.j[0].p);
+    } else {
+      R[i] = mul(R[i - 1], Rl);
+      p[i] = p[i - 1] + mul(R[i - 1], ld3(P.j[i].p));
+    }
+    const V3 z = mul(R[i], ld3(P.j[i].axis));
+    S[i] = SV{cross(p[i], z), z};
+  }
+#pragma unroll
+  for (int i = 0; i < NX; ++i) acc.Lx[i] = 0, acc.Lxxd[i] = 0;
+#pragma unroll
+  for (int i = 0; i < 2 * N; ++i) acc.Lu[i] = 0, acc.Luud[i] = 0;
+#pragma unroll
+  for (int i = 0; i < N * N; ++i) acc.Lqq[i] = 0;
+  return cost_terms<N, NU, true>(C, x, u, R, p, S, mref, acc);
+}
+
+// whether the two-phase evaluation applies: the dynamics must not need the kinematics
+template <int N>
+struct TwoPhase {
+  static constexpr bool value = (N == 2) && (ASLR_TWO_LINK != 0);
+};
+
+// the two halves of the compact record, element e at rec[e * stride]
+template <int N, int NU>
+ASLR_HD void crec_put_dyn(double* rec, const int stride, const KnotDeriv<N, NU>& kd) {
+  typedef CRec<N, NU> CR;
+#pragma unroll
+  for (int i = 0; i < 2 * N * 3 * N; ++i) rec[(size_t)(CR::AX + i) * stride] = kd.AX[i];
+#pragma unroll
+  for (int i = 0; i < 2 * N * NU; ++i) rec[(size_t)(CR::AU + i) * stride] = kd.AU[i];
+}
+template <int N, int NU>
+ASLR_HD void crec_put_cost(double* rec, const int stride, const CostAcc<N>& acc) {
+  typedef CRec<N, NU> CR;
+#pragma unroll
+  for (int i = 0; i < N * N; ++i) rec[(size_t)(CR::LQQ + i) * stride] = acc.Lqq[i];
+#pragma unroll
+  for (int i = 0; i < 4 * N; ++i) {
+    rec[(size_t)(CR::LXXD + i) * stride] = acc.Lxxd[i];
+    rec[(size_t)(CR::LX + i) * stride] = acc.Lx[i];
+  }
+#pragma unroll
+  for (int i = 0; i < NU; ++i) {
+    rec[(size_t)(CR::LUUD + i) * stride] = acc.Luud[i];
+    rec[(size_t)(CR::LU + i) * stride] = acc.Lu[i];
+  }
+  if (CR::SIZE > CR::LU + NU) rec[(size_t)(CR::LU + NU) * stride] = 0.0;
+}
+
 // knot_core + the whole record written straight to `rec` (contiguous)
 template <int N, int NU, bool VSA, bool DIFF>
 ASLR_HD void knot_eval(const DevProblem<N>& P, const DevCostSum<N>& C, const double dt, const double* x,

@@ -96,7 +96,7 @@ ASLR_HD void st_row(double* dst, const double* src) {
 // says whether this knot has a record to write.  `live` = false marks a padding thread of the last CTA.
 template <int N, int NU, bool VSA, bool STAGED>
 ASLR_HD bool calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, int t, bool live, KnotDeriv<N, NU>* kd,
-                           double* dt_out) {
+                           double* dt_out, double* stage2 = nullptr, int stage2_stride = 0) {
   constexpr int NX = 4 * N;
   typedef Rec<NX, NU> RC;
   if (!live) return false;
@@ -130,7 +130,15 @@ ASLR_HD bool calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, i
   const double* Kocp = a.K_ocp ? a.K_ocp + (size_t)b * N * N : nullptr;
   const double* mref = a.mref_ocp ? a.mref_ocp + (size_t)b * 12 : nullptr;
   const double dt = (t == T) ? P.dtT : P.dt;
-  if (STAGED) {
+  // two-phase evaluation (two-link models, compact record): the dynamics half now, its results parked in this
+  // thread's column of the shared-memory stage; the cost half after xnext and the gaps are out (knot.cuh)
+  const bool two_phase = STAGED && TwoPhase<N>::value && stage2 != nullptr;
+  if (two_phase) {
+    KnotDeriv<N, NU> dyn;
+    knot_core<N, NU, VSA, true, false>(P, t == T ? P.term : P.run, dt, x, u, Kocp, mref, xn, cost, dyn, nullptr, nullptr,
+                                       nullptr);
+    crec_put_dyn<N, NU>(stage2, stage2_stride, dyn);
+  } else if (STAGED) {
     *dt_out = dt;
     knot_core<N, NU, VSA, true>(P, t == T ? P.term : P.run, dt, x, u, Kocp, mref, xn, cost, *kd, nullptr, nullptr,
                                 nullptr);
@@ -139,7 +147,7 @@ ASLR_HD bool calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, i
     knot_eval<N, NU, VSA, true>(P, t == T ? P.term : P.run, dt, x, u, Kocp, mref, xn, cost, rec, nullptr, nullptr,
                                 nullptr);
   }
-  a.buf.knot_cost[(size_t)b * (T + 1) + t] = cost;
+  if (!two_phase) a.buf.knot_cost[(size_t)b * (T + 1) + t] = cost;
   if (t < T) {
     st_row<NX>(a.buf.xnext + ((size_t)b * T + t) * NX, xn);
   }
@@ -166,6 +174,11 @@ ASLR_HD bool calcdiff_body(const DevProblem<N>& P, const SolverArgs& a, int b, i
 #pragma unroll
       for (int i = 0; i < NX; ++i) fs[i] = 0.0;
     }
+  }
+  if (two_phase) {
+    CostAcc<N> acc;
+    a.buf.knot_cost[(size_t)b * (T + 1) + t] = knot_costs_diff<N, NU>(P, t == T ? P.term : P.run, x, u, mref, acc);
+    crec_put_cost<N, NU>(stage2, stage2_stride, acc);
   }
   return true;
 }
