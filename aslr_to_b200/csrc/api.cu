@@ -81,6 +81,7 @@ struct AslrProblem {
   // streams / events of the sub-batch pipeline.  `pipeline_ready` is set only after every one of them exists.
   bool pipeline_ready;
   int lanes, lane_min_ocps;  // ASLR_SOLVE_LANES / ASLR_LANE_MIN_OCPS, read from the environment once at create
+  int tail_max;              // ASLR_TAIL: largest number of running OCPs handed to the persistent straggler kernel (0 = off)
   int* pinned_counter;
   cudaEvent_t poll_event[2 * ASLR_MAX_LANES];
   cudaStream_t lane_stream[ASLR_MAX_LANES];  // [0] unused: sub-batch 0 runs on the caller's stream
@@ -188,6 +189,10 @@ int aslr_problem_create(const AslrProblemDesc* desc, AslrProblem** out) {
   p->pipeline_ready = false;
   p->lanes = env_int("ASLR_SOLVE_LANES", ASLR_SOLVE_LANES);
   p->lane_min_ocps = env_int("ASLR_LANE_MIN_OCPS", ASLR_LANE_MIN_OCPS);
+  // off by default: measured on the two never-converging OCPs of the headline batch it is no faster than the batch
+  // kernels (229 vs 223 us per iteration: the per-knot chains of K2 and K3 are the floor, not the launches)
+  p->tail_max = env_int("ASLR_TAIL", 0);
+  if (p->tail_max > ASLR_TAIL_MAX_OCPS) p->tail_max = ASLR_TAIL_MAX_OCPS;
   std::memset(&p->ws, 0, sizeof(p->ws));
   p->pinned_counter = nullptr;
   p->fork_event = nullptr;
@@ -464,8 +469,8 @@ int aslr_solve(const AslrProblem* pc, const AslrBatch* batch, const AslrSolverOp
   // waited for after the iterations up to poll k + 1 have been enqueued, so the GPU never idles on the
   // host round trip.  A sub-batch that finished costs at most `poll` extra iterations of empty kernels.
   int pending[ASLR_MAX_LANES], n_polls[ASLR_MAX_LANES], last_it[ASLR_MAX_LANES];
-  bool done[ASLR_MAX_LANES];
-  for (int k = 0; k < L; ++k) pending[k] = -1, n_polls[k] = 0, done[k] = false, last_it[k] = 0;
+  bool done[ASLR_MAX_LANES], tail_next[ASLR_MAX_LANES];
+  for (int k = 0; k < L; ++k) pending[k] = -1, n_polls[k] = 0, done[k] = false, last_it[k] = 0, tail_next[k] = false;
   bool all_done = false;
   for (it = 0; it < opts->maxiter && !all_done; ++it) {
     all_done = true;
@@ -473,6 +478,20 @@ int aslr_solve(const AslrProblem* pc, const AslrBatch* batch, const AslrSolverOp
       if (done[k]) continue;
       SolverArgs& ak = la[k];
       cudaStream_t sk = ls[k];
+      if (tail_next[k]) {
+        // Straggler regime (tail.cuh): the last poll showed few OCPs left in this sub-batch.  One persistent CTA per
+        // surviving OCP runs ALL remaining iterations; same device functions, bit-identical results, so it does not
+        // matter which iteration the switch happens at.
+        const int rc = p->fn.tail(p->dev, ak, it, sk);
+        if (rc == -2) return bail(cudaSuccess);
+        if (rc == 0) {
+          launches += 2;
+          done[k] = true;
+          last_it[k] = opts->maxiter;
+          continue;
+        }
+        tail_next[k] = false;  // not available for this horizon: carry on with the batch kernels
+      }
       ak.iter = it;
       ak.fuse_accept = 1;  // K4 rides on the trial-cost passes (kernels.cuh: linesearch_cost_kernel)
       if (p->fn.calcdiff(p->dev, ak, sk) || p->fn.backward(p->dev, ak, sk) || p->fn.rollout(p->dev, ak, sk))
@@ -484,7 +503,9 @@ int aslr_solve(const AslrProblem* pc, const AslrBatch* batch, const AslrSolverOp
         if (pending[k] >= 0) {  // consume the previous poll before its slot is reused
           cudaError_t e = cudaEventSynchronize(p->poll_event[2 * k + pending[k]]);
           if (e != cudaSuccess) return bail(e);
-          if (p->pinned_counter[2 * k + pending[k]] <= 0) done[k] = true;
+          const int left = p->pinned_counter[2 * k + pending[k]];
+          if (left <= 0) done[k] = true;
+          else if (p->fn.tail && left <= p->tail_max && it + 2 < opts->maxiter) tail_next[k] = true;
         }
         cudaError_t e = cudaMemcpyAsync(p->pinned_counter + 2 * k + slot, ak.buf.counters, sizeof(int),
                                         cudaMemcpyDeviceToHost, sk);

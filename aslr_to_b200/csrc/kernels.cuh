@@ -445,6 +445,10 @@ __global__ void __launch_bounds__(THREADS, ASLR_BWD_CTA_MINB) backward_cta_kerne
   backward_body<GrpCta<THREADS>, NX, NU>(g, smem, a, b, lim.lb, lim.ub, lim.has != 0, a.buf.counters);
 }
 
+}  // namespace aslr
+#include "tail.cuh"
+namespace aslr {
+
 // ------------------------------------------------------------------------------------ launchers
 struct Launchers {
   int (*knots)(const void* P, const KnotArgs& a, int diff, cudaStream_t s);
@@ -453,6 +457,9 @@ struct Launchers {
   int (*rollout)(const void* P, const SolverArgs& a, cudaStream_t s);
   int (*quasi_static)(const void* P, const KnotArgs& a, double* us, int maxiter, double tol, cudaStream_t s);
   int rollout_launches;  // kernels one call of `rollout` enqueues
+  // straggler regime (tail.cuh): all remaining iterations it0 .. maxiter - 1 of the OCPs still running, one persistent
+  // CTA each; null for the models without this path.  Two launches.
+  int (*tail)(const void* P, const SolverArgs& a, int it0, cudaStream_t s);
 };
 
 inline int launch_status() { return cudaGetLastError() == cudaSuccess ? 0 : -2; }
@@ -604,8 +611,28 @@ struct Launch {
     quasi_static_kernel<N, NU, VSA><<<(unsigned)((total + 63) / 64), 64, 0, s>>>(P, a, us, maxiter, tol);
     return launch_status();
   }
+  static constexpr bool HAS_TAIL = COMPACT && TwoPhase<N>::value;
+  static int tail(const void* Pv, const SolverArgs& a, int it0, cudaStream_t s) {
+    if constexpr (HAS_TAIL) {
+      const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
+      if (a.T + 1 > TailSmem<N, NU>::MAX_KNOTS || !a.ls_hdr) return -1;  // horizon too long for the CTA's shared memory
+      BoxLimits<NU> lim;
+      lim.has = P.has_limits;
+      for (int i = 0; i < NU; ++i) lim.lb[i] = P.u_lb[i], lim.ub[i] = P.u_ub[i];
+      constexpr size_t bytes = sizeof(double) * TailSmem<N, NU>::SIZE;
+      auto k = tail_kernel<N, NU, VSA>;
+      if (allow_smem(k, bytes)) return -2;
+      int* count = a.ls_hdr + 2;  // the work lists of the line search are idle from here on: reuse their storage
+      tail_list_kernel<<<1, 256, 0, s>>>(a, count, a.ls_list);
+      k<<<ASLR_TAIL_MAX_OCPS, ASLR_TAIL_THREADS, bytes, s>>>(P, a, lim, it0, count, a.ls_list);
+      return launch_status();
+    } else {
+      return -1;
+    }
+  }
   static Launchers table() {
-    return Launchers{&knots, &calcdiff, &backward, &rollout, &quasi_static, (N >= ASLR_ROLLC_MINN) ? 3 : 4};
+    return Launchers{&knots, &calcdiff, &backward, &rollout, &quasi_static, (N >= ASLR_ROLLC_MINN) ? 3 : 4,
+                     HAS_TAIL ? &tail : nullptr};
   }
 };
 

@@ -281,6 +281,34 @@ def test_sub_batch_pipeline_is_bit_identical_to_one_stream(BT, monkeypatch):
         assert np.array_equal(one["states"][k], cut["states"][k]), k
 
 
+@pytest.mark.parametrize("which", ["sea_batch", "double_pendulum", "two_dof_vsa_boxddp"])
+def test_straggler_kernel_is_bit_identical_to_the_batch_kernels(BT, monkeypatch, which):
+    """aslr_solve hands a sub-batch with few OCPs left to one persistent CTA per OCP (tail.cuh), at an iteration that
+    depends on when a poll comes back.  It calls the device functions of the batch kernels, so nothing may differ:
+    FDDP on 37 ragged OCPs, the double pendulum (regularisation retries in the backward pass, line searches that
+    fail) and the bounded VSA arm under BoxDDP (box QP in the sweep), each with the straggler path off and on."""
+    if which == "sea_batch":
+        w = W.sea_batch(37, seed=7)
+        w["T"], w["maxiter"] = 20, 25
+    elif which == "double_pendulum":
+        w = W.double_pendulum()
+        x0 = np.tile(np.atleast_2d(np.asarray(w["x0"], float)), (3, 1))
+        x0[:, 0] += np.array([0.0, -0.4, 0.3])
+        x0[:, 2] = x0[:, 0]
+        w = dict(w, x0=x0, maxiter=40)
+    else:
+        w = dict(W.two_dof_vsa_boxddp(), maxiter=60)
+    monkeypatch.setenv("ASLR_TAIL", "0")
+    off = gpu_solve(BT, w, T=w["T"])
+    monkeypatch.setenv("ASLR_TAIL", "128")
+    on = gpu_solve(BT, w, T=w["T"])
+    assert on["result"].kernel_launches < off["result"].kernel_launches  # the path was taken
+    for k in ("xs", "us", "Kgain", "kff", "Vx", "Vxx", "Qu", "fs", "log"):
+        assert np.array_equal(np.asarray(off[k]), np.asarray(on[k])), k
+    for k in ("iter", "status", "cost", "stop", "xreg", "steplength", "dV", "dVexp", "n_backward_retries", "n_logged"):
+        assert np.array_equal(off["states"][k], on["states"][k]), k
+
+
 def test_retries_inside_a_shared_warp_do_not_leak_between_ocps(BT):
     """The nx = 8 backward kernel runs four OCPs per warp in lockstep; an OCP whose sweep fails (Cholesky of
     Quu) repeats it with more regularisation while its neighbours ride along as ghosts.  Five double-pendulum
