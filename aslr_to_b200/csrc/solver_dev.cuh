@@ -368,12 +368,12 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
   for (int i = 0; i < NX; ++i) x[i] = a.x0[(size_t)b * NX + i];
   // the OCP's stiffness matrix is read once, not at every knot (a global load on the chain: 15 % of the stall
   // samples of the full-batch rollout were its first use)
+  // (unconditionally through the local array: with one possible source the compiler resolves knot_core's
+  // `Kocp ? Kocp[i] : P.K[i]` at compile time and the matrix lives in registers; a conditional re-pointing left it
+  // in local memory, one L1 round trip per knot on the chain)
   double Kreg[N * N];
-  if (Kocp) {
 #pragma unroll
-    for (int i = 0; i < N * N; ++i) Kreg[i] = Kocp[i];
-    Kocp = Kreg;
-  }
+  for (int i = 0; i < N * N; ++i) Kreg[i] = Kocp ? Kocp[i] : P.K[i];
   double cost_try = 0.0, dv = 0.0;
   bool ok = true;
   // Staged loads (CUDA kernel, small models): the gains, candidate state and controls of step t + 1 are copied
@@ -453,7 +453,7 @@ ASLR_HD void rollout_body(const DevProblem<N>& P, const SolverArgs& a, int b, in
     st_row<NU>(ut + (size_t)t * NU, u);
     double c;
     KnotDeriv<N, NU> unused;
-    knot_core<N, NU, VSA, false, false>(P, P.run, P.dt, x, u, Kocp, mref, xn, c, unused, nullptr, nullptr, nullptr);
+    knot_core<N, NU, VSA, false, false>(P, P.run, P.dt, x, u, Kreg, mref, xn, c, unused, nullptr, nullptr, nullptr);
     // crocoddyl's raiseIfNaN(|xnext|_inf): NaN, inf or >= 1e30.  The high word of |v| as an integer orders like |v|
     // (NaN and inf have the largest exponents), so one integer max and one compare decide
     unsigned mhi = 0u;

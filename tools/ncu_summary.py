@@ -3,7 +3,7 @@
 
   python tools/ncu_summary.py launches gpurun_out/launches.csv            > profiles/rNN_launches.md
   python tools/ncu_summary.py full gpurun_out/prof.ncu-rep [more.ncu-rep] > profiles/rNN_ncu_full.md
-  python tools/ncu_summary.py figures gpurun_out/prof.ncu-rep "what was captured"   -> profiles/ncu_figures.json
+  python tools/ncu_summary.py figures a.ncu-rep [b.ncu-rep] "what was captured"   -> profiles/ncu_figures.json
 
 `figures` writes the ncu-derived numbers bench.py quotes (DRAM bytes per launch, FP64 pipe utilisation, registers,
 spill sectors per kernel) together with the content hash of the kernel sources they were captured from; bench.py
@@ -107,12 +107,24 @@ def _unit_scale(u):
     return {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}.get(u, 1.0)
 
 
-def figures(path, what):
+def figures(paths, what):
     import json
     import os
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     sys.path.insert(0, root)
     import __graft_entry__ as ge
+    kernels = {}
+    for path in paths:
+        _figures_of(path, kernels)
+    out = {"source_hash": ge._source_hash(), "capture": what, "reports": [os.path.basename(q) for q in paths],
+           "kernels": kernels}
+    dst = os.path.join(root, "profiles", "ncu_figures.json")
+    with open(dst, "w") as f:
+        json.dump(out, f, indent=1)
+    print("wrote", dst, "for source hash", out["source_hash"][:12])
+
+
+def _figures_of(path, kernels):
     txt = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = [r for r in csv.reader(io.StringIO(txt)) if len(r) > 20]
     hdr, units, data = rows[0], rows[1], rows[2:]
@@ -126,7 +138,6 @@ def figures(path, what):
             return float(r[i].replace(",", "")) * _unit_scale(units[i])
         except ValueError:
             return None
-    kernels = {}
     for r in data:
         name = short_name(r[ki]).replace("aslr::", "")
         base = name.split("<")[0]
@@ -141,11 +152,6 @@ def figures(path, what):
                  "spill_sectors": (val(r, "l1tex__t_sectors_pipe_lsu_mem_local_op_ld.sum") or 0.0) +
                                   (val(r, "l1tex__t_sectors_pipe_lsu_mem_local_op_st.sum") or 0.0)}
         kernels.setdefault(base, entry)  # the first launch of each kernel in the capture
-    out = {"source_hash": ge._source_hash(), "capture": what, "report": os.path.basename(path), "kernels": kernels}
-    dst = os.path.join(root, "profiles", "ncu_figures.json")
-    with open(dst, "w") as f:
-        json.dump(out, f, indent=1)
-    print("wrote", dst, "for source hash", out["source_hash"][:12])
 
 
 def _fmt(s):
@@ -164,6 +170,6 @@ if __name__ == "__main__":
     if sys.argv[1] == "launches":
         launches(sys.argv[2])
     elif sys.argv[1] == "figures":
-        figures(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "")
+        figures([q for q in sys.argv[2:] if q.endswith(".ncu-rep")], " ".join(q for q in sys.argv[2:] if not q.endswith(".ncu-rep")))
     else:
         full(sys.argv[2:])
