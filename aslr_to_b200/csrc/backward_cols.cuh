@@ -285,7 +285,7 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
     // column j of a_x (zero for the v_m columns) and all of a_u
     double axc[H];
 #pragma unroll
-    for (int k = 0; k < H; ++k) axc[k] = (j < 3 * NQ) ? R[RC::AX + k * 3 * NQ + (j < 3 * NQ ? j : 0)] : 0.0;
+    for (int k = 0; k < H; ++k) axc[k] = (j < 3 * NQ) ? R[RC::AX + k * RC::AXS + (j < 3 * NQ ? j : 0)] : 0.0;
     double au[H][NU];
 #pragma unroll
     for (int k = 0; k < H; ++k) {
@@ -371,11 +371,11 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
 #pragma unroll
       for (int k = 0; k < H; ++k) {
         double ar[3 * NQ];
-        if constexpr ((3 * NQ) % 2 == 0) {
-          lds_row<3 * NQ>(R + RC::AX + k * 3 * NQ, ar);
-        } else {
+        {
+          double arp[RC::AXS];
+          lds_row<RC::AXS>(R + RC::AX + k * RC::AXS, arp);
 #pragma unroll
-          for (int c = 0; c < 3 * NQ; ++c) ar[c] = R[RC::AX + k * 3 * NQ + c];
+          for (int c = 0; c < 3 * NQ; ++c) ar[c] = arp[c];
         }
 #pragma unroll
         for (int c = 0; c < 3 * NQ; ++c) s[c] += a2[k] * ar[c];
@@ -625,7 +625,7 @@ __device__ void backward_body_cols(const GrpCols<NX>& g, double* sm, const Solve
   while (__any_sync(ASLR_FULL, need)) {
     bool ok;
     if constexpr (NX > 16)
-      ok = backward_sweep_rows<NX, NU>(g, sm, a, b, need, xreg, sums);  // no box QP: see the launcher
+      ok = backward_sweep_rows<NX, NU>(g, sm, a, b, need, xreg, sums, dt);  // no box QP: see the launcher
     else
       ok = backward_sweep_cols<NX, NU>(g, sm, a, b, need, u_lb, u_ub, box_limits, xreg, sums, dt);
     __syncwarp();

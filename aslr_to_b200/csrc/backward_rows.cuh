@@ -26,12 +26,14 @@ namespace aslr {
 
 template <int NX, int NU>
 struct RowsSmem {
-  static constexpr int RSZ = (Rec<NX, NU>::SIZE + 1) & ~1;
+  static constexpr int H = NX / 2;
+  static constexpr int RSZ = CRec<NX / 4, NU>::SIZE;  // the compact K1 -> K2 record (knot.cuh)
   static constexpr int REC = 0;
   static constexpr int VXX = RSZ;
   static constexpr int VT = VXX + NX * NX;  // unsymmetrised Vxx; earlier in the knot: FuV (NU x NX)
   static constexpr int FUV = VT;
-  static constexpr int KG = VT + NX * NX;
+  static constexpr int WS = VT + NX * NX;   // W = dt V'[0:H,:] + V'[H:,:]  (H x NX)
+  static constexpr int KG = WS + H * NX;
   static constexpr int VX = KG + NU * NX;
   static constexpr int QUU = VX + NX;
   static constexpr int FLAG = QUU + ((NU * NU + 1) & ~1);
@@ -41,35 +43,16 @@ struct RowsSmem {
   static constexpr int SIZE = (END > RED_END) ? END : RED_END;
 };
 
-// rows k of block BLK (q_l, q_m, v_l or v_m) of  Qxx[j,:] += A[j][k] Fx[k,:]  and  Qxu[j,:] += A[j][k] Fu[k,:];
-// the exact-zero pattern of Fx / Fu depends on the block only, so the k loop can stay rolled
-template <int NX, int NU, int BLK>
-__device__ __forceinline__ void qxx_block(const double* R, const double* AT, int j, double (&qxx)[NX],
-                                          double (&qxu)[NU]) {
-  typedef Rec<NX, NU> RC;
-  constexpr int NQ = NX / 4, K0 = BLK * NQ;
-#pragma unroll
-  for (int k = K0; k < K0 + NQ; ++k) {
-    const double aj = AT[k * NX + j];
-    double f[NX];
-    lds_row<NX>(R + RC::FX + k * NX, f);
-#pragma unroll
-    for (int c = 0; c < NX; ++c)
-      if (fx_nonzero<NX>(K0, c)) qxx[c] += aj * f[c];
-    if (fu_nonzero<NX, NU>(K0)) {
-#pragma unroll
-      for (int i = 0; i < NU; ++i) qxu[i] += aj * R[RC::FU + k * NU + i];
-    }
-  }
-}
-
 template <int NX, int NU>
 __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const SolverArgs& a, int b, bool live,
-                                    double xreg, double* sums /*[6]*/) {
-  static_assert(NX > 16 && NX <= 32 && NX % 2 == 0, "one OCP per warp");
+                                    double xreg, double* sums /*[6]*/, const double dt) {
+  static_assert(NX > 16 && NX <= 32 && NX % 4 == 0, "one OCP per warp");
   static_assert(NU <= 8, "the Cholesky factor of Quu is held in registers");
   typedef RowsSmem<NX, NU> CS;
-  typedef Rec<NX, NU> RC;
+  constexpr int NQ = NX / 4, H = 2 * NQ, AXW = 3 * NQ;
+  typedef CRec<NQ, NU> RC;
+  constexpr int AXS = RC::AXS;  // row stride of a_x in the record (even)  // what K1 left behind: a_x, a_u and the cost sums (knot.cuh)
+  const double dt2 = dt * dt;
   const int lane = g.lane;             // 0..31
   const bool pad = lane >= NX;         // duplicates of the last row, no stores
   const int j = pad ? NX - 1 : lane;
@@ -90,8 +73,15 @@ __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const Solv
   // ---- terminal node: Vxx = Lxx + xreg I, Vx = Lx (+ Vxx fs)
   {
     const double* rec = deriv + (size_t)T * RC::SIZE;
+    {
+      const double lxxd = rec[RC::LXXD + j];
 #pragma unroll
-    for (int c = 0; c < NX; ++c) vrow[c] = rec[RC::LXX + j * NX + c] + ((c == j) ? xreg : 0.0);
+      for (int c = 0; c < NX; ++c) {
+        double l = (c == j) ? lxxd : 0.0;  // record_put: diagonal part, plus the (q_l, q_l) block
+        if (c < NQ) l += (j < NQ) ? rec[RC::LQQ + (j < NQ ? j : 0) * NQ + c] : 0.0;
+        vrow[c] = l + ((c == j) ? xreg : 0.0);
+      }
+    }
     vx = rec[RC::LX + j];
     double w = 0.0;
     if (any_gaps) {
@@ -115,6 +105,8 @@ __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const Solv
     if (!pad) {
       sts_row<NX>(sm + CS::VXX + j * NX, vrow);
       sm[CS::VX + j] = vx;
+#pragma unroll
+      for (int k = 0; k < H; ++k) sm[CS::WS + k * NX + j] = fma(dt, vrow[k], vrow[H + k]);  // column j of W
     }
   }
   cp_async_drain();
@@ -133,80 +125,99 @@ __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const Solv
   for (int t = T - 1; t >= 0; --t) {
     double fsj = 0.0;
     if (any_gaps) fsj = fs[t * NX + j];
-    // ---- A[j,:] = sum_k Fx[k][j] Vxx'[k,:] ; Qx[j] = Lx[j] + Fx[:,j]^T Vx'
-    // (k loops are rolled: the fully unrolled knot body was ~4300 instructions = 68 KB, and seven warps at
-    //  different places of it made instruction fetch the top stall reason)
+    // ---- The discrete Jacobians are never formed (see backward_cols.cuh for the algebra): with H = 2n,
+    // Fx = I + [dt^2 a_x + dt S; dt a_x], Fu = [dt^2 a_u; dt a_u], every product collapses onto the H rows of a_x / a_u,
+    //     Fx^T V' = V' + dt (a_x^T W + S^T V'[0:H,:]),   W = dt V'[0:H,:] + V'[H:,:] (parked by the previous knot),
+    //     A Fx = A + a2 a_x + dt [0 | A[:,0:H]],          a2 = dt (dt A[:,0:H] + A[:,H:]).
+    // Half the multiply-adds of the two 28^3 products, and a 4 KB record per knot instead of 16 KB.
+    const bool lo = j < H;
+    const int jr = lo ? j : j - H;
+    // ---- A[j,:] ; Qx[j] = Lx[j] + (Fx^T Vx')[j]
+    // (the k loop is rolled: seven warps at different places of a fully unrolled body made instruction fetch the
+    //  top stall reason in round 1)
     double arow[NX], qx;
     {
+      double acc[NX];
 #pragma unroll
-      for (int c = 0; c < NX; ++c) arow[c] = 0.0;
+      for (int c = 0; c < NX; ++c) acc[c] = 0.0;
       double s = 0.0;
-#pragma unroll 4
-      for (int k = 0; k < NX; ++k) {
-        const double f = R[RC::FX + k * NX + j];
-        double v[NX];
-        lds_row<NX>(sm + CS::VXX + k * NX, v);
+      const bool has = j < AXW;  // the v_m columns of a_x are zero
+#pragma unroll 2
+      for (int k = 0; k < H; ++k) {
+        const double f = has ? R[RC::AX + k * AXS + (has ? j : 0)] : 0.0;
+        double w[NX];
+        lds_row<NX>(sm + CS::WS + k * NX, w);
 #pragma unroll
-        for (int c = 0; c < NX; ++c) arow[c] += f * v[c];
-        s += f * sm[CS::VX + k];
+        for (int c = 0; c < NX; ++c) acc[c] += f * w[c];
+        s += f * fma(dt, sm[CS::VX + k], sm[CS::VX + H + k]);  // wv[k] = dt Vx'[k] + Vx'[H + k]
       }
-      qx = R[RC::LX + j] + s;
+      double v[NX];
+      lds_row<NX>(sm + CS::VXX + jr * NX, v);  // row j - H of V' for the v rows (S^T V'); unused by the q rows
+#pragma unroll
+      for (int c = 0; c < NX; ++c) arow[c] = fma(dt, lo ? acc[c] : acc[c] + v[c], vrow[c]);
+      qx = R[RC::LX + j] + fma(dt, lo ? s : s + sm[CS::VX + jr], vx);
     }
-    // ---- FuV[:,j] = sum_k Fu[k][:] Vxx'[k][j] (own row, by symmetry) -> shared memory for the Quu entries
+    // ---- FuV[:,j] = (Fu^T V')[:,j] = dt a_u^T W[:,j], W[:,j] = dt V'[j,0:H] + V'[j,H:] (own row, by symmetry)
     {
       double fuv[NU];
 #pragma unroll
       for (int i = 0; i < NU; ++i) fuv[i] = 0.0;
 #pragma unroll
-      for (int k = 0; k < NX; ++k) {
+      for (int k = 0; k < H; ++k) {
         if (fu_nonzero<NX, NU>(k)) {
+          const double w2 = fma(dt, vrow[k], vrow[H + k]);
 #pragma unroll
-          for (int i = 0; i < NU; ++i) fuv[i] += R[RC::FU + k * NU + i] * vrow[k];
+          for (int i = 0; i < NU; ++i) fuv[i] += R[RC::AU + k * NU + i] * w2;
         }
       }
       if (!pad) {
 #pragma unroll
-        for (int i = 0; i < NU; ++i) sm[CS::FUV + i * NX + j] = fuv[i];
+        for (int i = 0; i < NU; ++i) sm[CS::FUV + i * NX + j] = dt * fuv[i];
       }
     }
-    // ---- Qu = Lu + Fu^T Vx': lane i < NU computes entry i, then everybody gets all of them
+    // ---- Qu = Lu + Fu^T Vx' = Lu + dt a_u^T wv: lane i < NU computes entry i, then everybody gets all of them
     double qu[NU];
     {
       const int i = (lane < NU) ? lane : 0;
       double s = 0.0;
 #pragma unroll
-      for (int k = 0; k < NX; ++k)
-        if (fu_nonzero<NX, NU>(k)) s += R[RC::FU + k * NU + i] * sm[CS::VX + k];
-      const double mine = R[RC::LU + i] + s;
+      for (int k = 0; k < H; ++k)
+        if (fu_nonzero<NX, NU>(k)) s += R[RC::AU + k * NU + i] * fma(dt, sm[CS::VX + k], sm[CS::VX + H + k]);
+      const double mine = fma(dt, s, R[RC::LU + i]);
 #pragma unroll
       for (int r = 0; r < NU; ++r) qu[r] = __shfl_sync(ASLR_FULL, mine, r);
     }
-    // ---- Qxx[j,:] = Lxx[j,:] + A[j,:] Fx, Qxu[j,:] = Lxu[j,:] + A[j,:] Fu
-    // A[j][k] has to be indexed by the loop variable: park the row in shared memory, transposed (element
-    // (k, lane) -> conflict-free), on top of Vxx', which nobody reads any more once every lane is here
+    // ---- Qxx[j,:] = Lxx[j,:] + (A Fx)[j,:], Qxu[j,:] = (A Fu)[j,:]   (Lxu = 0)
     double qxx[NX], qxu[NU];
     {
-      __syncwarp();
-      double* AT = sm + CS::VXX;
-      if (!pad) {
+      double a2[H];
 #pragma unroll
-        for (int c = 0; c < NX; ++c) AT[c * NX + j] = arow[c];
-      }
-      __syncwarp();
+      for (int k = 0; k < H; ++k) a2[k] = dt * fma(dt, arow[k], arow[H + k]);
+      double sacc[AXS];
 #pragma unroll
-      for (int c = 0; c < NX; ++c) qxx[c] = 0.0;
+      for (int c = 0; c < AXS; ++c) sacc[c] = 0.0;
 #pragma unroll
       for (int i = 0; i < NU; ++i) qxu[i] = 0.0;
-      qxx_block<NX, NU, 0>(R, AT, j, qxx, qxu);
-      qxx_block<NX, NU, 1>(R, AT, j, qxx, qxu);
-      qxx_block<NX, NU, 2>(R, AT, j, qxx, qxu);
-      qxx_block<NX, NU, 3>(R, AT, j, qxx, qxu);
-      double l[NX];
-      lds_row<NX>(R + RC::LXX + j * NX, l);
 #pragma unroll
-      for (int c = 0; c < NX; ++c) qxx[c] = l[c] + qxx[c];
+      for (int k = 0; k < H; ++k) {
+        double ar[AXS];
+        lds_row<AXS>(R + RC::AX + k * AXS, ar);
 #pragma unroll
-      for (int i = 0; i < NU; ++i) qxu[i] = R[RC::LXU + j * NU + i] + qxu[i];
+        for (int c = 0; c < AXW; ++c) sacc[c] += a2[k] * ar[c];
+        if (fu_nonzero<NX, NU>(k)) {
+#pragma unroll
+          for (int i = 0; i < NU; ++i) qxu[i] += a2[k] * R[RC::AU + k * NU + i];
+        }
+      }
+      const double lxxd = R[RC::LXXD + j];
+#pragma unroll
+      for (int c = 0; c < NX; ++c) {
+        double l = (c == j) ? lxxd : 0.0;
+        if (c < NQ) l += (j < NQ) ? R[RC::LQQ + (j < NQ ? j : 0) * NQ + c] : 0.0;
+        double q = arow[c] + ((c < AXW) ? sacc[c < AXW ? c : 0] : 0.0);
+        if (c >= H) q = fma(dt, arow[c >= H ? c - H : 0], q);
+        qxx[c] = l + q;
+      }
     }
     __syncwarp();  // FuV complete
     // ---- Quu = Luu + (FuV Fu + ureg I): the NU x NU entries shared out over the 32 lanes
@@ -218,8 +229,9 @@ __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const Solv
         double s = 0.0;
 #pragma unroll
         for (int k = 0; k < NX; ++k)
-          if (fu_nonzero<NX, NU>(k)) s += sm[CS::FUV + i * NX + k] * R[RC::FU + k * NU + l];
-        sm[CS::QUU + e] = R[RC::LUU + e] + (s + ((i == l) ? xreg : 0.0));
+          if (fu_nonzero<NX, NU>(k))
+            s += sm[CS::FUV + i * NX + k] * ((k < H ? dt2 : dt) * R[RC::AU + (k < H ? k : k - H) * NU + l]);  // Fu[k][l]
+        sm[CS::QUU + e] = ((i == l) ? R[RC::LUUD + i] : 0.0) + (s + ((i == l) ? xreg : 0.0));
       }
     }
     __syncwarp();  // Quu complete; nothing below reads the record: fetch the next one under the gains
@@ -304,10 +316,12 @@ __device__ bool backward_sweep_rows(const GrpCols<NX>& g, double* sm, const Solv
         return false;
       }
     }
-    // ---- the next knot reads Vxx, Vx from shared memory (every lane is past its reads of them)
+    // ---- the next knot reads Vxx, Vx, W from shared memory (every lane is past its reads of them)
     if (!pad) {
       sts_row<NX>(sm + CS::VXX + j * NX, vrow);
       sm[CS::VX + j] = vx;
+#pragma unroll
+      for (int k = 0; k < H; ++k) sm[CS::WS + k * NX + j] = fma(dt, vrow[k], vrow[H + k]);  // column j of W
     }
     // ---- store (the pointers walk backwards with t)
     if (live && !pad) {

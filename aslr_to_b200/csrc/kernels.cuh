@@ -43,7 +43,7 @@
 #endif
 #ifndef ASLR_BWD_ROWS
 #define ASLR_BWD_ROWS 1       // nx = 28, nu <= 8 backward pass: row-per-lane sweep, one OCP per warp (backward_rows.cuh)
-#define ASLR_BWD_ROWS_MINB 7  // resident CTAs (= OCPs) per SM: 31.6 KB of shared memory each
+#define ASLR_BWD_ROWS_MINB 10  // resident CTAs (= OCPs) per SM: 22 KB of shared memory each with the compact record
 #endif
 #ifndef ASLR_BWD_GS
 #define ASLR_BWD_GS 16  // lanes per OCP in the nx = 8 backward pass
@@ -429,11 +429,11 @@ __global__ void __launch_bounds__(NX * GROUPS) backward_cols_kernel(const Solver
 
 // row-per-lane sweep for nx = 28 (backward_rows.cuh): one warp = one OCP = one CTA
 template <int NX, int NU>
-__global__ void __launch_bounds__(32, ASLR_BWD_ROWS_MINB) backward_rows_kernel(const SolverArgs a) {
+__global__ void __launch_bounds__(32, ASLR_BWD_ROWS_MINB) backward_rows_kernel(const SolverArgs a, const double dt) {
   extern __shared__ double smem[];
   const int lane = threadIdx.x;
   GrpCols<NX> g{lane, (NX == 32) ? 0xffffffffu : ((1u << NX) - 1u)};
-  backward_body_cols<NX, NU>(g, smem, a, (int)blockIdx.x, nullptr, nullptr, false, a.buf.counters, 0.0);
+  backward_body_cols<NX, NU>(g, smem, a, (int)blockIdx.x, nullptr, nullptr, false, a.buf.counters, dt);
 }
 
 // CTA per OCP (nx = 28)
@@ -495,9 +495,15 @@ struct Launch {
   // whether aslr_solve's K1 -> K2 hand-over uses the compact record CRec<N, NU> (knot.cuh): the row-per-lane
   // backward kernel of nx = 8 reads it; every other backward kernel still reads the dense record
   static constexpr bool COMPACT = (NX == 8) && (ASLR_BWD_COLS != 0);
+  // nx = 28, nu <= 8: the one-OCP-per-warp sweep (backward_rows.cuh) reads the compact record as well; it has no box
+  // QP, so SolverBoxDDP with control limits stays with the CTA-per-OCP sweep and the dense record (a run-time choice)
+  static constexpr bool ROWS = (NX > 16 && NX <= 32 && NU <= 8 && ASLR_BWD_ROWS != 0 && N <= ASLR_K1_STAGE_MAXN);
+  static bool rows_path(const DevProblem<N>& P, const SolverArgs& a) {
+    return ROWS && !(a.opts.kind == ASLR_SOLVER_BOXDDP && P.has_limits);
+  }
   // shared-memory staging of the coalesced record stores
   static size_t stage_bytes(int threads, bool compact = false) {
-    const int wd = compact ? RecParts<RecSize<N, NU, COMPACT>::SIZE>::WARP_DOUBLES : RecParts<Rec<NX, NU>::SIZE>::WARP_DOUBLES;
+    const int wd = compact ? RecParts<CRec<N, NU>::SIZE>::WARP_DOUBLES : RecParts<Rec<NX, NU>::SIZE>::WARP_DOUBLES;
     return (N <= ASLR_K1_STAGE_MAXN) ? sizeof(double) * wd * (threads / 32) : 0;
   }
   static int knots(const void* Pv, const KnotArgs& a, int diff, cudaStream_t s) {
@@ -519,10 +525,17 @@ struct Launch {
     const DevProblem<N>& P = *static_cast<const DevProblem<N>*>(Pv);
     const long total = (long)a.B * (a.T + 1);
     const int threads = 128;
+    const unsigned blocks = (unsigned)((total + threads - 1) / threads);
+    if constexpr (ROWS) {
+      if (rows_path(P, a)) {
+        if (allow_smem(solver_calcdiff_kernel<N, NU, VSA, true>, stage_bytes(threads, true))) return -2;
+        solver_calcdiff_kernel<N, NU, VSA, true><<<blocks, threads, stage_bytes(threads, true), s>>>(P, a);
+        return launch_status();
+      }
+    }
     if (N <= ASLR_K1_STAGE_MAXN)
       if (allow_smem(solver_calcdiff_kernel<N, NU, VSA, COMPACT>, stage_bytes(threads, COMPACT))) return -2;
-    solver_calcdiff_kernel<N, NU, VSA, COMPACT>
-        <<<(unsigned)((total + threads - 1) / threads), threads, stage_bytes(threads, COMPACT), s>>>(P, a);
+    solver_calcdiff_kernel<N, NU, VSA, COMPACT><<<blocks, threads, stage_bytes(threads, COMPACT), s>>>(P, a);
     return launch_status();
   }
   // grid of the trial-cost kernel.  Pass 0 (alpha = 1 of every running OCP: the list is full whenever the batch
@@ -578,13 +591,13 @@ struct Launch {
       auto k = backward_cols_kernel<NX, NU, GROUPS>;
       if (allow_smem(k, slice * GROUPS)) return -2;
       k<<<(a.B + GROUPS - 1) / GROUPS, NX * GROUPS, slice * GROUPS, s>>>(a, lim, P.dt);
-    } else if constexpr (NX > 16 && NX <= 32 && NU <= 8 && ASLR_BWD_ROWS) {
+    } else if constexpr (ROWS) {
       // (the box QP of SolverBoxDDP stays with the CTA-per-OCP sweep)
-      if (!(a.opts.kind == ASLR_SOLVER_BOXDDP && P.has_limits)) {
+      if (rows_path(P, a)) {
         constexpr size_t bytes = sizeof(double) * RowsSmem<NX, NU>::SIZE;
         auto k = backward_rows_kernel<NX, NU>;
         if (allow_smem(k, bytes)) return -2;
-        k<<<a.B, 32, bytes, s>>>(a);
+        k<<<a.B, 32, bytes, s>>>(a, P.dt);
         return launch_status();
       }
       constexpr int THREADS = ASLR_BWD_CTA_THREADS;

@@ -637,8 +637,9 @@ ASLR_HD void record_put(double* rec, const int stride, const double dt, const Kn
 //   (8, 2): 56 doubles = 448 B instead of 174 = 1392 B;   (28, 7): 512 doubles instead of 2044.
 template <int N, int NU>
 struct CRec {
-  static constexpr int AX = 0;                      // a_x     2N x 3N
-  static constexpr int AU = AX + 2 * N * 3 * N;     // a_u     2N x NU
+  static constexpr int AX = 0;                      // a_x     2N x 3N, rows AXS apart (even: 16-byte row loads)
+  static constexpr int AXS = (3 * N + 1) & ~1;
+  static constexpr int AU = AX + 2 * N * AXS;       // a_u     2N x NU
   static constexpr int LQQ = AU + 2 * N * NU;       // dense block of Lxx on (q_l, q_l)   N x N
   static constexpr int LXXD = LQQ + N * N;          // diagonal part of Lxx   4N
   static constexpr int LUUD = LXXD + 4 * N;         // diagonal of Luu        NU
@@ -651,7 +652,10 @@ template <int N, int NU, int LO, int HI>
 ASLR_HD void crec_put(double* rec, const int stride, const KnotDeriv<N, NU>& kd) {
   typedef CRec<N, NU> CR;
 #pragma unroll
-  for (int i = 0; i < 2 * N * 3 * N; ++i) ASLR_PUT(CR::AX + i, kd.AX[i]);
+  for (int r = 0; r < 2 * N; ++r) {
+#pragma unroll
+    for (int c = 0; c < CR::AXS; ++c) ASLR_PUT(CR::AX + r * CR::AXS + c, (c < 3 * N) ? kd.AX[r * 3 * N + (c < 3 * N ? c : 0)] : 0.0);
+  }
 #pragma unroll
   for (int i = 0; i < 2 * N * NU; ++i) ASLR_PUT(CR::AU + i, kd.AU[i]);
 #pragma unroll
@@ -749,7 +753,11 @@ template <int N, int NU>
 ASLR_HD void crec_put_dyn(double* rec, const int stride, const KnotDeriv<N, NU>& kd) {
   typedef CRec<N, NU> CR;
 #pragma unroll
-  for (int i = 0; i < 2 * N * 3 * N; ++i) rec[(size_t)(CR::AX + i) * stride] = kd.AX[i];
+  for (int r = 0; r < 2 * N; ++r) {
+#pragma unroll
+    for (int c = 0; c < CR::AXS; ++c)
+      rec[(size_t)(CR::AX + r * CR::AXS + c) * stride] = (c < 3 * N) ? kd.AX[r * 3 * N + (c < 3 * N ? c : 0)] : 0.0;
+  }
 #pragma unroll
   for (int i = 0; i < 2 * N * NU; ++i) rec[(size_t)(CR::AU + i) * stride] = kd.AU[i];
 }
