@@ -339,21 +339,42 @@ __global__ void __launch_bounds__(128) linesearch_cost_kernel(const __grid_const
   // the rounds (at T = 100: one round of the knot-cost chain instead of four).
   if (count <= (int)gridDim.x && a.T + 1 <= ASLR_COST_CTA_MAXT) {
     __shared__ double kc[ASLR_COST_CTA_MAXT];
-    if ((int)blockIdx.x < count) {
-      const int id = list[blockIdx.x];
-      const int b = id / ASLR_NUM_ALPHAS, ai = id % ASLR_NUM_ALPHAS;
-      double* tr = a.buf.trial + ((size_t)b * ASLR_NUM_ALPHAS + ai) * 4;
-      const bool ran = tr[2] != 0.0;
-      if (ran)
-        for (int t = threadIdx.x; t <= a.T; t += blockDim.x) kc[t] = trial_knot_cost<N, NU, VSA>(P, a, b, ai, t);
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        if (ran) {
-          double total = 0.0;
-          for (int t = 0; t <= a.T; ++t) total += kc[t];
-          trial_cost_finish(a, b, ai, total);
+    // Very short list in pass 0 (ten CTAs per listed OCP fit in the grid): an OCP whose ten step lengths were all
+    // rolled out already gets all ten costed NOW, one CTA each, and the tenth to finish runs the accept decision --
+    // the second rollout phase and cost pass then have nothing to do for it.  (The lazy evaluation of the other nine
+    // only pays while the GPU is full; here they run beside alpha = 1 at no cost in time.)
+    constexpr bool SINGLE_PHASE = (N >= ASLR_ROLLC_MINN);  // the lane-cooperative rollout runs all ten at once
+    const bool wide = (pass == 0) && ((long)count * ASLR_NUM_ALPHAS <= (long)gridDim.x);
+    const int e = wide ? (int)blockIdx.x / ASLR_NUM_ALPHAS : (int)blockIdx.x;
+    if (e < count) {
+      const int id = list[e];
+      const int b = id / ASLR_NUM_ALPHAS;
+      const bool all_ten = wide && (SINGLE_PHASE || !rollout_narrow(a.buf.state[b]));
+      const int ai = wide ? (int)blockIdx.x % ASLR_NUM_ALPHAS : id % ASLR_NUM_ALPHAS;
+      if (ai == 0 || !wide || all_ten) {
+        double* tr = a.buf.trial + ((size_t)b * ASLR_NUM_ALPHAS + ai) * 4;
+        const bool ran = tr[2] != 0.0;
+        if (ran)
+          for (int t = threadIdx.x; t <= a.T; t += blockDim.x) kc[t] = trial_knot_cost<N, NU, VSA>(P, a, b, ai, t);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+          if (ran) {
+            double total = 0.0;
+            for (int t = 0; t <= a.T; ++t) total += kc[t];
+            trial_cost_finish(a, b, ai, total);
+          }
+          if (all_ten) {
+            AslrOcpState& s = a.buf.state[b];
+            __threadfence();  // this trial's record before the count
+            if (atomicAdd(&s.ls_done, 1) + 1 == ASLR_NUM_ALPHAS) {
+              __threadfence();  // the other trials' records after the count
+              s.ls_done = 0;
+              if (a.fuse_accept) accept_body(a, b, a.buf.counters);
+            }
+          } else {
+            linesearch_after_cost(a, b, pass, tr);
+          }
         }
-        linesearch_after_cost(a, b, pass, tr);
       }
     }
     if (pass == 1 && blockIdx.x == 0 && threadIdx.x == 0) a.ls_hdr[0] = 0;
