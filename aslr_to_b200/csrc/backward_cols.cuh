@@ -18,6 +18,9 @@
 // (the Cholesky chain under the Qxx products).
 // Device-only (shuffles); the host emulation keeps using backward_sweep.
 #pragma once
+#ifdef ASLR_K2_CLK
+#include <cstdio>
+#endif
 
 namespace aslr {
 
@@ -253,6 +256,20 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
   double* pVxx = a.buf.Vxx ? a.buf.Vxx + ((size_t)b * (T + 1) + (T - 1)) * NX * NX + j * NX : nullptr;
   const double* psrc = deriv + (size_t)(T - 2) * RC::SIZE;  // the record staged during knot T - 1
   int cur = 0;
+#ifdef ASLR_K2_CLK
+  long long clk[14], clk_prev;
+  for (int i = 0; i < 14; ++i) clk[i] = 0;
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(clk_prev)::"memory");
+#define ASLR_CLK(i)                                                        \
+  {                                                                        \
+    long long now_;                                                        \
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_)::"memory");        \
+    clk[i] += now_ - clk_prev;                                             \
+    clk_prev = now_;                                                       \
+  }
+#else
+#define ASLR_CLK(i)
+#endif
   for (int t = T - 1; t >= 0; --t) {
     const double* R = sm + (cur ? CS::REC1 : CS::REC0);
     if (t >= 1) stage_record<RC::SIZE, NX>(sm + (cur ? CS::REC0 : CS::REC1), psrc, j);
@@ -302,6 +319,7 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
         for (int i = 0; i < NU; ++i) au[k][i] = R[RC::AU + k * NU + i];
       }
     }
+    ASLR_CLK(0);
     // ---- A[j,:] = (Fx^T V')[j,:]
     double arow[NX];
     {
@@ -320,6 +338,7 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
 #pragma unroll
       for (int c = 0; c < NX; ++c) arow[c] = fma(dt, lo ? s[c] : s[c] + v[c], vrow[c]);
     }
+    ASLR_CLK(1);
     // ---- wv, Qx[j] = Lx[j] + (Fx^T Vx')[j], Qu = Lu + Fu^T Vx' (every lane)
     double qx, qu[NU];
     {
@@ -344,6 +363,7 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
         qu[i] = fma(dt, s2, R[RC::LU + i]);
       }
     }
+    ASLR_CLK(2);
     // ---- FuV[:,j] = (Fu^T V')[:,j] = dt a_u^T W[:,j],  W[:,j] = dt V'[j,0:H] + V'[j,H:] (own row, by symmetry)
     double fuv[NU];
     {
@@ -359,6 +379,7 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
         fuv[i] = dt * s;
       }
     }
+    ASLR_CLK(3);
     // ---- Qxx[j,:] = Lxx[j,:] + (A Fx)[j,:], Qxu[j,:] = (A Fu)[j,:]   (Lxu = 0: no cost of the menu couples x and u)
     double qxx[NX], qxu[NU];
     {
@@ -399,6 +420,7 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
         qxu[i] = s2;
       }
     }
+    ASLR_CLK(4);
     // ---- Quu = Luu + (FuV Fu + ureg I): butterfly sum of the lanes' terms FuV[:,j] Fu[j,:]
     double quu[NU * NU];
     {
@@ -414,6 +436,7 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
         }
       }
     }
+    ASLR_CLK(5);
     // ---- computeGains: K[:,j] and k
     double kcol[NU], kf[NU];
     {
@@ -457,6 +480,7 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
         }
       }
     }
+    ASLR_CLK(6);
     // ---- Quuk = Quu k ; Vx[j] = Qx[j] + K[:,j]^T Quuk - 2 K[:,j]^T Qu
     double quuk[NU];
 #pragma unroll
@@ -472,6 +496,7 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
       for (int k = 0; k < NU; ++k) s1 += kcol[k] * quuk[k], s2 += kcol[k] * qu[k];
       vx = (qx + s1) - 2.0 * s2;
     }
+    ASLR_CLK(7);
     // ---- exchange the gains; Vtmp[j,:] = Qxx[j,:] - Qxu[j,:] K
 #pragma unroll
     for (int r = 0; r < NU; ++r) sm[CS::KG + r * NX + j] = kcol[r];
@@ -491,6 +516,7 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
 #pragma unroll
       for (int c = 0; c < NX; ++c) vt[c] = qxx[c] - s[c];
     }
+    ASLR_CLK(8);
     // ---- symmetrise (lane j needs column j of Vtmp) + xreg, NaN / inf check
     sts_row<NX>(sm + CS::VT + j * NX, vt);
     g.sync();
@@ -508,6 +534,7 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
       for (int k = 0; k < NX; ++k) w += vrow[k] * fsv[k];
       vx += w;
     }
+    ASLR_CLK(9);
     mhi = max(mhi, mag_hi(vx));
     if (__any_sync(ASLR_FULL, mhi >= ASLR_BAD_HI)) {  // rare: run the exact test
       bool bad = isnan(vx) || bad_value(fabs(vx));
@@ -515,11 +542,13 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
       for (int c = 0; c < NX; ++c) bad = bad || isnan(vrow[c]) || bad_value(fabs(vrow[c]));
       if ((__ballot_sync(ASLR_FULL, bad) & mask) != 0u && live) failed = true, live = false;
     }
+    ASLR_CLK(10);
     // ---- the next knot reads Vxx, Vx and W from shared memory (safe: every lane is past its reads of them)
     sts_row<NX>(sm + CS::VXX + j * NX, vrow);
     sm[CS::VX + j] = vx;
 #pragma unroll
     for (int k = 0; k < 2 * NQ; ++k) sm[CS::FXF + k * NX + j] = fma(dt, vrow[k], vrow[2 * NQ + k]);  // column j of W
+    ASLR_CLK(11);
     // ---- store (the pointers walk backwards with t)
     if (live) {
 #pragma unroll
@@ -557,10 +586,17 @@ __device__ bool backward_sweep_cols(const GrpCols<NX>& g, double* sm, const Solv
 #pragma unroll
       for (int k = 0; k < NX; ++k) dgf -= __shfl_sync(ASLR_FULL, p, k, NX), dqf += __shfl_sync(ASLR_FULL, q, k, NX);
     }
+    ASLR_CLK(12);
     cp_async_drain();
     g.sync();
+    ASLR_CLK(13);
     cur ^= 1;
   }
+#ifdef ASLR_K2_CLK
+  if (b == 0 && j == 0 && blockIdx.x == 0)
+    printf("K2CLK T=%d per knot: loads %lld arow %lld qx %lld fuv %lld qxx %lld quu %lld gains %lld vx %lld kg+vt %lld sym %lld vote %lld sts %lld stg %lld wait %lld\n", T,
+           clk[0] / T, clk[1] / T, clk[2] / T, clk[3] / T, clk[4] / T, clk[5] / T, clk[6] / T, clk[7] / T, clk[8] / T, clk[9] / T, clk[10] / T, clk[11] / T, clk[12] / T, clk[13] / T);
+#endif
   if (j == 0) sums[0] = stop, sums[1] = d1, sums[2] = d2, sums[3] = dgf, sums[4] = dqf;
   return !failed;
 }
